@@ -1,0 +1,274 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the population self-replication hot path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (config.workload = "ww22_self_application"): per GPU, 2^24 WeightwiseNeuralNetwork(width=2, depth=2)
+nets with Keras-default (glorot-uniform) weights, 100 unconditional self-applications each -- the shape of
+BASELINE.json's configs[0]/[4] (code/setups/applying-fixpoints.py: 100 x self_attack per net) at population
+scale.  One "step" = one pass of the kernel over one arena of 2^24 nets = 1.68e9
+self-applications.  Every timed step works on its own fresh arena (0.94 GB each, far larger than the 126 MB
+L2), all resident in HBM before the timed region starts.
+
+  value    whole-job self-applications/s, device-timed (CUDA events), max over ranks
+  e2e      same metric through the host API with HOST inputs: pinned-host -> device copy of the step's
+           14-float records, kernel + fused classification, class counters back to the host, double-buffered
+  roofline the kernel against the FP32 issue roofline (bound "fp32"): achieved = 392 algorithmic FLOP per
+           self-application / kernel time; peak = an FFMA-only probe kernel measured live on the same GPU
+  cpu_baseline  the oracle's SIMD/OpenMP WW(2,2) path on the box's host cores, on a bounded sample
+
+--impl reference: times the CPU implementation alone (the oracle port -- the reference's own Keras path needs
+TensorFlow 1.x, which is not installable here or on the box), rank 0 only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "self-replicating-neural-networks_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+N_NETS = 1 << 24
+N_STEPS = 100
+FLOP_PER_SELF_APP = 392.0       # 14 points x 14 MAC x 2
+FP32_INSTR_PER_SELF_APP = 224.0  # pinned operation order: 14 x (8 FFMA + 6 FMUL + 2 FADD)
+BYTES_PER_NET = 112.0           # 56 B read + 56 B write per resident episode
+METRIC = "net self-applications/sec"
+UNIT = "self-applications/s"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7),
+                              ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_port_rate(n_nets, seconds):
+    """Oracle WW(2,2) SIMD/OpenMP path, repeated for ~`seconds`; returns (self-applications/s, cores, sample)."""
+    import oracle
+    rng = np.random.default_rng(0)
+    lim = np.array([1.0] * 8 + [np.sqrt(1.5)] * 4 + [np.sqrt(2.0)] * 2)
+    w0 = (rng.uniform(-1, 1, (n_nets, 14)) * lim).astype(np.float32)
+    oracle.ww22_self_apply_fast(w0.copy(), 2)  # warm-up (thread pool, page faults)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        w = w0.copy()
+        t1 = time.perf_counter()
+        oracle.ww22_self_apply_fast(w, N_STEPS)
+        done += 1
+        el = time.perf_counter() - t0
+        if el >= seconds:
+            break
+    dt = time.perf_counter() - t0
+    return n_nets * N_STEPS * done / dt, oracle.num_threads(), "%d x (2^%d nets x %d steps)" % (
+        done, int(np.log2(n_nets)), N_STEPS)
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    n = 1 << 20
+    import oracle
+    rng = np.random.default_rng(0)
+    lim = np.array([1.0] * 8 + [np.sqrt(1.5)] * 4 + [np.sqrt(2.0)] * 2)
+    w0 = (rng.uniform(-1, 1, (n, 14)) * lim).astype(np.float32)
+    for _ in range(args.warmup):
+        oracle.ww22_self_apply_fast(w0.copy(), N_STEPS)
+    bufs = [w0.copy() for _ in range(args.steps)]
+    t0 = time.perf_counter()
+    for b in bufs:
+        oracle.ww22_self_apply_fast(b, N_STEPS)
+    dt = time.perf_counter() - t0
+    val = n * N_STEPS * args.steps / dt
+    cores = oracle.num_threads()
+    sample = "per step 2^20 of the 2^24 nets x %d self-applications" % N_STEPS
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ww22_self_application", "nets_per_gpu": N_NETS, "self_applications_per_net": N_STEPS,
+                   "net": "WeightwiseNeuralNetwork(width=2, depth=2)", "l2": "inputs larger than L2"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference Keras/TensorFlow-1.x path unavailable on this box; timed the oracle port "
+                "(same arithmetic, SIMD + OpenMP over nets)"}), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--nets", type=int, default=N_NETS, help="nets per GPU (default 2^24)")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import srnn_engine as eng
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.nets
+    K, W = args.steps, args.warmup
+    desc = eng.make_desc(eng.KIND_WW, 2, 2)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # fresh arenas, one per step (capped by memory: reuse round-robin beyond the cap)
+    free = torch.cuda.mem_get_info()[0]
+    cap = max(2, int(free * 0.6 // (n * 56)))
+    R = min(K + W, cap)
+    arenas = [eng.Population(desc, n).init(seed=1000 + r, slot0=rank * n) for r in range(R)]
+    torch.cuda.synchronize()
+
+    # ---- FP32 issue-rate probe = roofline denominator (lane-FFMA/s)
+    probe = max(eng.fp32_probe(variant=0), eng.fp32_probe(variant=1))
+
+    # ---- device-resident timing
+    for s in range(W):
+        arenas[s % R].self_apply(N_STEPS)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_begin.record()
+    for s in range(K):
+        evs[s][0].record()
+        arenas[(W + s) % R].self_apply(N_STEPS)
+        evs[s][1].record()
+    t_end.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    total_ms = t_begin.elapsed_time(t_end)
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+    t = torch.tensor([total_ms, kern_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, kern_ms = t.tolist()
+    value = world * n * N_STEPS * K / (total_ms * 1e-3)
+
+    # ---- end to end: pinned host records -> device -> kernel + classify -> counters to host, double-buffered
+    del arenas[2:]
+    torch.cuda.empty_cache()
+    host = torch.empty((n, 14), dtype=torch.float32).pin_memory()
+    lim = np.array([1.0] * 8 + [1.5 ** .5] * 4 + [2 ** .5] * 2)
+    host.copy_(torch.from_numpy((np.random.default_rng(rank).uniform(-1, 1, (n, 14)) * lim).astype(np.float32)))
+    cnt_host = torch.zeros((2, 5), dtype=torch.int64).pin_memory()
+    copy_stream, comp_stream = torch.cuda.Stream(), torch.cuda.Stream()
+    copied = [torch.cuda.Event() for _ in range(2)]
+    freed = [torch.cuda.Event() for _ in range(2)]
+
+    def e2e_steps(count):
+        for s in range(count):
+            b = s % 2
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(freed[b])
+                arenas[b].w.copy_(host, non_blocking=True)
+                copied[b].record(copy_stream)
+            with torch.cuda.stream(comp_stream):
+                comp_stream.wait_event(copied[b])
+                out = arenas[b].self_apply(N_STEPS, want_counters=True, eps=1e-4)
+                cnt_host[b].copy_(out["counters"], non_blocking=True)
+                freed[b].record(comp_stream)
+        comp_stream.synchronize()
+
+    for b in range(2):
+        freed[b].record(comp_stream)
+    e2e_steps(W)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps(K)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * N_STEPS * K / t.item()
+
+    if rank == 0:
+        achieved_tf = FLOP_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / 1e12
+        peak_tf = probe * 2.0 / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "ww22_self_application", "nets_per_gpu": n, "self_applications_per_net": N_STEPS,
+                       "net": "WeightwiseNeuralNetwork(width=2, depth=2)", "init": "glorot_uniform (Philox)",
+                       "fresh_arenas": R, "l2": "inputs larger than L2 (0.94 GB arena per step, new arena each step)",
+                       "parallelism": "population sharded by net index, no data-path collective"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": 40},
+            "gpu_launches": K,
+            "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": achieved_tf / peak_tf, "traffic": None,
+                         "kernel": "self_apply_fixed_kernel<WW(2,2)>", "kernel_ms": kern_ms,
+                         "peak_source": "FFMA-only probe kernel measured live (MEASURED_PEAKS.json has no FP32 entry)",
+                         "issue_frac": FP32_INSTR_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / probe,
+                         "hbm_gbs": BYTES_PER_NET * n / (kern_ms * 1e-3) / 1e9},
+        }
+        if world == 1:
+            v, cores, sample = cpu_port_rate(1 << 20, args.cpu_seconds)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

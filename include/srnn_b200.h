@@ -1,0 +1,129 @@
+/* srnn_b200.h -- C ABI of libsrnn_b200.so, the B200 (sm_100a) population engine.
+ *
+ * The reference (illiumst/self-replicating-neural-networks) has no FFI: its "operator API" is the
+ * Python class surface of code/network.py / code/soup.py / code/experiment.py.  Each entry point
+ * below replaces the inner loops of the cited reference methods for a whole population at once;
+ * the Python facade (self-replicating-neural-networks_b200/network.py, soup.py, experiment.py)
+ * binds them with ctypes and keeps the reference's class names and call signatures.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every `float* w` is a DEVICE pointer to a population arena of
+ *    records (include/srnn_types.h): w[i*ld + k].  Index arrays, outputs and counters are DEVICE
+ *    pointers too unless the comment says "host".
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream).  Calls are asynchronous on
+ *    that stream; the library allocates nothing and never frees caller memory.
+ *  - return value: SRNN_OK (0) or an SRNN_ERR_* code; srnn_last_error_string() gives the text.
+ *    NaN / Inf in the data is a domain state ("divergent"), never an error.
+ *  - arithmetic: FP32, flush-to-zero, operation order and FMA placement pinned to the reference's
+ *    committed Keras trajectories (DESIGN.md "Pinned arithmetic").
+ *  - net shapes are compile-time instantiated (srnn_shape_supported()); others return SRNN_ERR_SHAPE.
+ */
+#ifndef SRNN_B200_H
+#define SRNN_B200_H
+
+#include "srnn_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* library / device plumbing (no reference counterpart) */
+int         srnn_version(void);
+const char *srnn_last_error_string(void);
+int         srnn_set_device(int device);
+/* fills d->n_weights from (kind, width, depth, aggregates): the Keras layer stacks of
+ * code/network.py:226-230 (WW), :329-333 (AGG), :531-535 (RNN) */
+int         srnn_desc_init(srnn_net_desc *d);
+int         srnn_shape_supported(const srnn_net_desc *d);
+
+/* NeuralNetwork.apply_to_network / attack / fuck (code/network.py:112-122) over a list of pairs, with
+ * WeightwiseNeuralNetwork.apply_to_weights :265-279, AggregatingNeuralNetwork.apply_to_weights :359-386,
+ * RecurrentNeuralNetwork.apply_to_weights :544-564 as the operator:
+ *     out[out_idx[p]] <- f_{op[op_idx[p]]}( in[in_idx[p]] ),  p = 0..n-1     (NULL idx = identity p)
+ * attack(a -> v): op=a, in=out=v.  fuck: op=self, in=other, out=self.  Pairs run in parallel: within
+ * one call no record may be written by one pair and read or written by another. */
+int srnn_apply(const srnn_net_desc *d, const float *op_w, int64_t op_ld, const int32_t *op_idx,
+               const float *in_w, int64_t in_ld, const int32_t *in_idx,
+               float *out_w, int64_t out_ld, const int32_t *out_idx, int64_t n, void *stream);
+
+/* NeuralNetwork.self_attack(n_steps) (code/network.py:124-127) for every net, weights register-resident
+ * for the whole run; mode SRNN_RUN_UNTIL adds FixpointExperiment.run_net's stop rule
+ * (code/experiment.py:70-77: stop when is_diverged() or is_fixpoint()).
+ *   steps_out  (nullable) int32[n]: self-applications executed per net
+ *   cls_out    (nullable) uint8[n]: FixpointExperiment.count class of the final weights (experiment.py:79-91)
+ *   counters   (nullable) int64[5]: class histogram, ACCUMULATED into (caller zeroes)
+ *   traj       (nullable) float[n_steps][n][ld]: state after each executed step (ParticleDecorator.save_state,
+ *              network.py:193-198); slots of steps never executed are left untouched */
+int srnn_self_apply(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t n_steps, int32_t mode,
+                    double eps, int32_t with_fix_sec, int32_t *steps_out, uint8_t *cls_out, int64_t *counters,
+                    float *traj, void *stream);
+
+/* Soup.count / FixpointExperiment.count decision list (code/soup.py:89-103, code/experiment.py:79-91):
+ * is_diverged (network.py:133) -> is_fixpoint(1) (:140-157) -> is_zero (:136) -> is_fixpoint(2).
+ * with_fix_sec = 0 gives the setups' soup-level count without the fix_sec branch (mixed-soup.py:27-53).
+ * flags_out (nullable) uint8[n]: bit0 is_diverged, bit1 is_zero, bit2 is_fixpoint(1), bit3 is_fixpoint(2). */
+int srnn_classify(const srnn_net_desc *d, const float *w, int64_t ld, int64_t n, double eps, int32_t with_fix_sec,
+                  uint8_t *cls_out, uint8_t *flags_out, int64_t *counters, void *stream);
+
+/* TrainingNeuralNetworkDecorator.train (code/network.py:613-618) when teacher_w == NULL, learn_from
+ * (:620-626) otherwise: n_epochs Keras epochs of SGD(lr) on MSE with batch_size 1, fused forward +
+ * backward + update, weights register-resident.  Samples = compute_samples() of the net itself
+ * (re-frozen at the start of every epoch, :615) or of teacher record teacher_idx[i] (NULL = i).
+ *   perm_mode  SRNN_PERM_NONE | SRNN_PERM_EXPLICIT (perm = uint8[n_epochs][n_samples], device) |
+ *              SRNN_PERM_PHILOX (per (slot0+i, epoch0+e) Fisher-Yates)
+ *   loss_out   (nullable) double[n]: Keras History 'loss' of the LAST epoch */
+int srnn_train(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t n_epochs, float lr,
+               int32_t perm_mode, const uint8_t *perm, uint64_t seed, uint64_t slot0, uint64_t epoch0,
+               const float *teacher_w, int64_t teacher_ld, const int32_t *teacher_idx, double *loss_out,
+               void *stream);
+
+/* Soup.generate_particle (code/soup.py:37-40) = fresh Keras model: Dense kernels glorot_uniform, SimpleRNN
+ * recurrent kernels orthogonal (Keras defaults implied by network.py:227-230, :330-333, :532-535).
+ * Deterministic: record idx[p] (NULL = p) is a pure function of (seed, slot0 + index, generation). */
+int srnn_init(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, const int32_t *idx, uint64_t seed,
+              uint64_t slot0, uint32_t generation, void *stream);
+
+/* code/setups/known-fixpoint-variation.py: vary() :37-46 + trial loop :60-89 for n trials at one noise
+ * level.  base = the fixpoint's n_weights floats (HOST pointer, copied by value into the launch).
+ *   time_to_vergence / time_as_fixpoint (nullable) int32[n]      = the script's ys / zs
+ *   hist (nullable) int64[2][max_steps+1]: histograms of ys and zs, ACCUMULATED into
+ *   w_out (nullable) float[n][ld]: final weights */
+int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double scale, uint32_t level,
+             int32_t max_steps, double eps, uint64_t seed, uint64_t slot0, int32_t *time_to_vergence,
+             int32_t *time_as_fixpoint, int64_t *hist, float *w_out, int64_t ld, void *stream);
+
+/* Soup.evolve (code/soup.py:51-87), exact order: one generation, particles visited in index order,
+ * every write visible to later particles.  att / lrn = int64[n] target index or -1 per particle (drawn
+ * by the host in the reference's order, soup.py:56-63).  Outputs (nullable): action uint8[n]
+ * (SRNN_ACT_*), loss double[n] (last train epoch, NaN if none), logged float[n][ld] = the weights
+ * particle.save_state (soup.py:87) logs for the old particle.  Meant for the setups' soups (10-100 nets). */
+int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n,
+                      const int64_t *att, const int64_t *lrn, uint64_t seed, uint64_t gen, uint8_t *action,
+                      double *loss, float *logged, void *stream);
+
+/* Soup.evolve, snapshot-synchronous generation for large / sharded soups (DESIGN.md "Soup modes"): every
+ * partner is read from `snap`, the start-of-generation arena of ALL n_total particles (after the
+ * per-generation all-gather when sharded); this call owns particles [slot0, slot0+n) and writes their
+ * new records to w_out (w_out must not alias snap).  Pairings are Philox draws of (seed, slot, gen) in the
+ * reference's per-particle order; a victim hit several times applies attackers in ascending index.
+ *   scratch  int32[n_total + n]: attack lists (head[n] + next[n_total]); contents need no initialisation
+ *   action (nullable) uint8[n], loss (nullable) double[n], dead (nullable) uint8[n] (1 = respawned) */
+int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const float *snap, int64_t snap_ld,
+                   int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed,
+                   uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream);
+
+/* ParticleDecorator uid allocation for respawned particles (code/network.py:167-171, soup.py:78,83):
+ * uid[i] <- uid_base + (number of dead[j] != 0 with j < i) for every dead i; *n_dead_out (device int64,
+ * nullable) receives the total.  block_tmp = int64[ceil(n/1024) + 1] scratch. */
+int srnn_assign_uids(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *uid, int64_t *block_tmp,
+                     int64_t *n_dead_out, void *stream);
+
+/* FP32 issue-rate probe: an FFMA-only kernel (independent chains, operands in registers) used as the
+ * measured roofline denominator for the register-resident kernels (MEASURED_PEAKS.json has no FP32 entry).
+ * Runs `iters` x 64 FFMA per thread over grid x block threads; out = float[grid*block] sink. */
+int srnn_fp32_probe(float *out, int32_t grid, int32_t block, int32_t iters, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

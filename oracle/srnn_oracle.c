@@ -400,6 +400,7 @@ static void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, in
                 for (int q = 0; q < 4 && c + q < n; ++q) v[c + q] = 2.0f * u01f(x[q]) - 1.0f;
             }
             for (int c = 0; c < n; ++c) nn = nn + v[c] * v[c];
+            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; break; } /* 1x1 orthogonal = +-1 exactly */
             if (nn > 1.0f || nn < 1e-4f) continue;           /* outside ball / too short: reject  */
             for (int p = 0; p < r; ++p) {                     /* remove components along earlier rows */
                 float dot = 0.f;
@@ -408,7 +409,7 @@ static void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, in
             }
             nn = 0.f;
             for (int c = 0; c < n; ++c) nn = nn + v[c] * v[c];
-            if (nn < 1e-6f) continue;
+            if (nn < 1e-2f) continue;
             float inv = 1.0f / sqrtf(nn);
             for (int c = 0; c < n; ++c) U[r * n + c] = v[c] * inv;
             break;

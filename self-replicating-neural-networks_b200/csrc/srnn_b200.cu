@@ -1,0 +1,841 @@
+// srnn_b200.cu -- kernels and C-ABI entry points of libsrnn_b200.so (sm_100a only).
+//
+// Build (see __graft_entry__.build):
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -ftz=true
+//        -prec-div=true -prec-sqrt=true -Xcompiler -fPIC -shared -o libsrnn_b200.so srnn_b200.cu
+//
+// Execution model: one thread owns one net.  A CTA of 256 threads stages its tile of 256 contiguous
+// records (256 * n_weights floats) between HBM and shared memory with fully coalesced accesses, then
+// every thread pulls its own record into registers, runs the whole episode (100 self-applications,
+// 1000 SGD epochs, one soup generation ...) without touching memory again, and the tile goes back the
+// same way.  FP32 CUDA cores only: the per-net matrices are 4x2 / 2x2 / 2x1 -- nothing a tcgen05 tile
+// could chew on -- so the bound is the FP32 issue rate for iterated kernels and HBM for one-pass ones.
+#include <cuda_runtime.h>
+
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/srnn_b200.h"
+#include "srnn_device.cuh"
+
+namespace srnn {
+
+constexpr int BS = 256;  // threads per CTA = records per tile
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+static int fail(int code, const char *fmt, const char *detail = "") {
+    snprintf(g_err, sizeof g_err, fmt, detail);
+    return code;
+}
+static int check_launch(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(e));
+        return SRNN_ERR_CUDA;
+    }
+    return SRNN_OK;
+}
+
+// R6: predicates compare f32 values with the f64 epsilon.  For an f32 value d:  d >= eps  <=>  d >= eps_ge
+// (smallest f32 >= eps) and d <= eps  <=>  d <= eps_le (largest f32 <= eps), so the kernels compare in f32.
+struct Eps { float ge, le; };
+static int make_eps(double eps, Eps *e) {
+    if (!(eps >= (double)FLT_MIN) || !(eps <= (double)FLT_MAX))
+        return fail(SRNN_ERR_ARG, "epsilon must be a normal float32 magnitude (FLT_MIN <= eps <= FLT_MAX)%s");
+    float f = (float)eps;
+    e->ge = ((double)f < eps) ? nextafterf(f, INFINITY) : f;
+    e->le = ((double)f > eps) ? nextafterf(f, 0.0f) : f;
+    return SRNN_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ tile staging
+// Shared-memory record stride is NW|1 (odd) so the per-thread reads are bank-conflict free.
+template <int NW> __host__ __device__ constexpr int tile_stride() { return NW | 1; }
+
+template <int NW>
+__device__ __forceinline__ void tile_load(const float *__restrict__ w, int64_t ld, int64_t base, int64_t n,
+                                          float *tile, float *reg) {
+    const int tid = threadIdx.x;
+    const int cnt = (int)min((int64_t)BS, n - base);
+    if (ld == NW) {
+        const float *src = w + base * NW;
+        for (int e = tid; e < cnt * NW; e += BS) tile[(e / NW) * tile_stride<NW>() + (e % NW)] = __ldg(src + e);
+        __syncthreads();
+        if (tid < cnt) {
+#pragma unroll
+            for (int k = 0; k < NW; ++k) reg[k] = tile[tid * tile_stride<NW>() + k];
+        }
+    } else if (tid < cnt) {
+        const float *src = w + (base + tid) * ld;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) reg[k] = __ldg(src + k);
+    }
+}
+template <int NW>
+__device__ __forceinline__ void tile_store(float *__restrict__ w, int64_t ld, int64_t base, int64_t n, float *tile,
+                                           const float *reg) {
+    const int tid = threadIdx.x;
+    const int cnt = (int)min((int64_t)BS, n - base);
+    if (ld == NW) {
+        __syncthreads();  // tile may still be read by slower threads of a previous phase
+        if (tid < cnt) {
+#pragma unroll
+            for (int k = 0; k < NW; ++k) tile[tid * tile_stride<NW>() + k] = reg[k];
+        }
+        __syncthreads();
+        float *dst = w + base * NW;
+        for (int e = tid; e < cnt * NW; e += BS) dst[e] = tile[(e / NW) * tile_stride<NW>() + (e % NW)];
+    } else if (tid < cnt) {
+        float *dst = w + (base + tid) * ld;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) dst[k] = reg[k];
+    }
+}
+template <int NW>
+__device__ __forceinline__ void record_load(const float *__restrict__ w, int64_t ld, int64_t i, float *reg) {
+    const float *src = w + i * ld;
+#pragma unroll
+    for (int k = 0; k < NW; ++k) reg[k] = __ldg(src + k);
+}
+template <int NW>
+__device__ __forceinline__ void record_store(float *__restrict__ w, int64_t ld, int64_t i, const float *reg) {
+    float *dst = w + i * ld;
+#pragma unroll
+    for (int k = 0; k < NW; ++k) dst[k] = reg[k];
+}
+
+__device__ __forceinline__ void block_histogram(int cls, bool active, unsigned int *sh /*[5]*/,
+                                                unsigned long long *counters) {
+    if (threadIdx.x < 5) sh[threadIdx.x] = 0;
+    __syncthreads();
+    if (active) atomicAdd(&sh[cls], 1u);
+    __syncthreads();
+    if (threadIdx.x < 5 && sh[threadIdx.x]) atomicAdd(&counters[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
+}
+
+// ================================================================================================ K1 self-application
+// FAST: n_steps unconditional self-applications, nothing else in the loop (the benchmarked kernel).
+template <class S>
+__global__ void __launch_bounds__(BS) self_apply_fixed_kernel(float *__restrict__ w, int64_t ld, int64_t n,
+                                                              int n_steps) {
+    __shared__ float tile[BS * tile_stride<S::NW>()];
+    const int64_t base = (int64_t)blockIdx.x * BS;
+    float a[S::NW], b[S::NW];
+    tile_load<S::NW>(w, ld, base, n, tile, a);
+    if (base + threadIdx.x < n) {
+        int s = 0;
+        for (; s + 2 <= n_steps; s += 2) {  // ping-pong: no register copies between steps
+            net_apply<S>(a, a, b);
+            net_apply<S>(b, b, a);
+        }
+        if (s < n_steps) {
+            net_apply<S>(a, a, b);
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) a[k] = b[k];
+        }
+    }
+    tile_store<S::NW>(w, ld, base, n, tile, a);
+}
+
+// GENERAL: optional run_net stop rule, per-step trajectory, fused classification.
+template <class S>
+__global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restrict__ w, int64_t ld, int64_t n,
+                                                                int n_steps, int mode, Eps eps, int with_fix_sec,
+                                                                int *__restrict__ steps_out,
+                                                                uint8_t *__restrict__ cls_out,
+                                                                unsigned long long *counters,
+                                                                float *__restrict__ traj) {
+    __shared__ float tile[BS * tile_stride<S::NW>()];
+    __shared__ unsigned int hist[5];
+    const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
+    const bool active = i < n;
+    float cur[S::NW], nxt[S::NW];
+    tile_load<S::NW>(w, ld, base, n, tile, cur);
+    int it = 0, cls = SRNN_CLS_OTHER;
+    if (active) {
+        net_apply<S>(cur, cur, nxt);  // look-ahead: is_fixpoint's application IS the next self_attack
+        while (it < n_steps) {
+            if (mode == SRNN_RUN_UNTIL && (is_diverged<S::NW>(cur) || is_close<S::NW>(nxt, cur, eps.ge))) break;
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
+            ++it;
+            if (traj) record_store<S::NW>(traj + (int64_t)(it - 1) * n * ld, ld, i, cur);
+            net_apply<S>(cur, cur, nxt);
+        }
+        if (steps_out) steps_out[i] = it;
+        if (cls_out || counters) {
+            cls = classify_with<S>(cur, nxt, eps.ge, eps.le, with_fix_sec);
+            if (cls_out) cls_out[i] = (uint8_t)cls;
+        }
+    }
+    if (counters) block_histogram(cls, active, hist, counters);
+    tile_store<S::NW>(w, ld, base, n, tile, cur);
+}
+
+// ================================================================================================ K2/K3/K4 apply
+template <class S>
+__global__ void __launch_bounds__(BS) apply_kernel(const float *op_w, int64_t op_ld,
+                                                   const int32_t *__restrict__ op_idx, const float *in_w,
+                                                   int64_t in_ld, const int32_t *__restrict__ in_idx, float *out_w,
+                                                   int64_t out_ld, const int32_t *__restrict__ out_idx, int64_t n) {
+    const int64_t p = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (p >= n) return;
+    float op[S::NW], in[S::NW], out[S::NW];
+    {   // op / in may alias out (attack on self): plain loads, no read-only path
+        const float *so = op_w + (op_idx ? (int64_t)op_idx[p] : p) * op_ld;
+        const float *si = in_w + (in_idx ? (int64_t)in_idx[p] : p) * in_ld;
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) { op[k] = so[k]; in[k] = si[k]; }
+    }
+    net_apply<S>(op, in, out);
+    record_store<S::NW>(out_w, out_ld, out_idx ? out_idx[p] : p, out);
+}
+
+// ================================================================================================ K6 classify
+template <class S>
+__global__ void __launch_bounds__(BS) classify_kernel(const float *__restrict__ w, int64_t ld, int64_t n, Eps eps,
+                                                      int with_fix_sec, uint8_t *__restrict__ cls_out,
+                                                      uint8_t *__restrict__ flags_out, unsigned long long *counters) {
+    __shared__ float tile[BS * tile_stride<S::NW>()];
+    __shared__ unsigned int hist[5];
+    const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
+    const bool active = i < n;
+    float cur[S::NW], nxt[S::NW];
+    tile_load<S::NW>(w, ld, base, n, tile, cur);
+    int cls = SRNN_CLS_OTHER;
+    if (active) {
+        net_apply<S>(cur, cur, nxt);
+        cls = classify_with<S>(cur, nxt, eps.ge, eps.le, with_fix_sec);
+        if (cls_out) cls_out[i] = (uint8_t)cls;
+        if (flags_out) {
+            float nn[S::NW];
+            net_apply<S>(cur, nxt, nn);
+            flags_out[i] = (uint8_t)((is_diverged<S::NW>(cur) ? 1 : 0) | (is_zero<S::NW>(cur, eps.le) ? 2 : 0) |
+                                     (is_close<S::NW>(nxt, cur, eps.ge) ? 4 : 0) |
+                                     (is_close<S::NW>(nn, cur, eps.ge) ? 8 : 0));
+        }
+    }
+    if (counters) block_histogram(cls, active, hist, counters);
+}
+
+// ================================================================================================ K7 init / respawn
+template <class S>
+__global__ void __launch_bounds__(BS) init_kernel(float *__restrict__ w, int64_t ld, int64_t n,
+                                                  const int32_t *__restrict__ idx, uint64_t seed, uint64_t slot0,
+                                                  uint32_t gen, Limits lim) {
+    const int64_t p = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (p >= n) return;
+    const int64_t i = idx ? idx[p] : p;
+    float cur[S::NW];
+    init_net<S>(seed, slot0 + (uint64_t)i, gen, lim, cur);
+    record_store<S::NW>(w, ld, i, cur);
+}
+
+// ================================================================================================ K5 train / learn_from
+// SGD scratch columns live in dynamic shared memory: tgt float[NW][BS] | ord uint8[NS][BS] | codes float[3*NW]
+template <class S> __host__ __device__ constexpr size_t sgd_smem_bytes(int threads) {
+    return sizeof(float) * S::NW * threads + (size_t)((S::NS * threads + 15) / 16 * 16) + sizeof(float) * 3 * S::NW;
+}
+template <class S>
+__device__ __forceinline__ SgdScratch sgd_scratch(unsigned char *smem, int threads) {
+    SgdScratch sc;
+    sc.tgt = reinterpret_cast<float *>(smem) + threadIdx.x;
+    sc.ord = smem + sizeof(float) * S::NW * threads + threadIdx.x;
+    sc.stride = threads;
+    float *codes = reinterpret_cast<float *>(smem + sizeof(float) * S::NW * threads + (S::NS * threads + 15) / 16 * 16);
+    if (threadIdx.x == 0) fill_codes<S>(codes);
+    sc.codes = codes;
+    return sc;
+}
+
+template <class S>
+__global__ void __launch_bounds__(BS) train_kernel(float *__restrict__ w, int64_t ld, int64_t n, int n_epochs,
+                                                   float lr, int perm_mode, const uint8_t *__restrict__ perm,
+                                                   uint64_t seed, uint64_t slot0, uint64_t epoch0,
+                                                   const float *__restrict__ teacher_w, int64_t teacher_ld,
+                                                   const int32_t *__restrict__ teacher_idx,
+                                                   double *__restrict__ loss_out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ float tile[BS * tile_stride<S::NW>()];
+    const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
+    const bool active = i < n;
+    SgdScratch sc = sgd_scratch<S>(smem, BS);
+    float cur[S::NW];
+    tile_load<S::NW>(w, ld, base, n, tile, cur);
+    __syncthreads();  // codes visible
+    if (active) {
+        if (teacher_w) {
+            const float *src = teacher_w + (teacher_idx ? (int64_t)teacher_idx[i] : i) * teacher_ld;
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = src[k];
+        }
+        double loss = 0.0;
+        const bool ordered = S::NS > 1 && perm_mode != SRNN_PERM_NONE;
+        for (int e = 0; e < n_epochs; ++e) {
+            if (!teacher_w) {  // targets frozen at the start of the epoch, code/network.py:615
+#pragma unroll
+                for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+            }
+            if (ordered) {
+                if (perm_mode == SRNN_PERM_EXPLICIT) {
+                    for (int q = 0; q < S::NS; ++q) sc.ord[q * sc.stride] = perm[(int64_t)e * S::NS + q];
+                } else {
+                    philox_perm<S::NS>(seed, slot0 + (uint64_t)i, epoch0 + (uint64_t)e, sc.ord, sc.stride);
+                }
+            }
+            loss = train_epoch<S>(cur, sc, ordered, lr);
+        }
+        if (loss_out) loss_out[i] = loss;
+    }
+    tile_store<S::NW>(w, ld, base, n, tile, cur);
+}
+
+// ================================================================================================ K9 known-fixpoint variation
+struct BaseNet { float v[SRNN_MAX_WEIGHTS]; };
+
+template <class S>
+__global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, double scale, uint32_t level,
+                                                 int max_steps, Eps eps, uint64_t seed, uint64_t slot0,
+                                                 int *__restrict__ ys, int *__restrict__ zs,
+                                                 unsigned long long *hist, float *__restrict__ w_out, int64_t ld) {
+    const int64_t i = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (i >= n) return;
+    float cur[S::NW], nxt[S::NW];
+    // vary(), known-fixpoint-variation.py:37-46: float64 perturbation stored as float32
+#pragma unroll
+    for (int k = 0; k < S::NW; ++k) {
+        const U4 x = rng4(seed, ST_KFV, slot0 + (uint64_t)i, level, (uint32_t)k);
+        const double mag = __dmul_rn(u01d(x.y), scale);
+        const double b = (double)basenet.v[k];
+        cur[k] = (float)(u01d(x.x) < 0.5 ? __dadd_rn(b, mag) : __dsub_rn(b, mag));
+    }
+    // trial loop :69-82; after each self_attack the fixpoint test's application is the next step's result
+    int tts = 0, taf = 0;
+    bool still = true;
+    net_apply<S>(cur, cur, nxt);
+    for (int st = 0; st < max_steps; ++st) {
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
+        if (is_zero<S::NW>(cur, eps.le) || is_diverged<S::NW>(cur)) break;
+        net_apply<S>(cur, cur, nxt);
+        if (is_close<S::NW>(nxt, cur, eps.ge)) {
+            if (still) ++taf;
+            else still = true;
+        } else {
+            still = false;
+        }
+        ++tts;
+    }
+    if (ys) ys[i] = tts;
+    if (zs) zs[i] = taf;
+    if (hist) {
+        atomicAdd(&hist[tts], 1ull);
+        atomicAdd(&hist[(max_steps + 1) + taf], 1ull);
+    }
+    if (w_out) record_store<S::NW>(w_out, ld, i, cur);
+}
+
+// ================================================================================================ K8 soup
+struct SoupP {
+    double attacking_rate, learn_from_rate;
+    int train, severity, remove_divergent, remove_zero, perm_mode;
+    float lr;
+    Eps eps;
+};
+
+__device__ __forceinline__ void soup_draw(const SoupP &p, uint64_t seed, uint64_t slot, uint64_t gen,
+                                          int64_t n_total, int64_t *att, int64_t *lrn) {
+    const U4 x = rng4(seed, ST_SOUP, slot, (uint32_t)gen, (uint32_t)(gen >> 32));
+    *att = (u01d(x.x) < p.attacking_rate) ? (int64_t)(((uint64_t)x.y * (uint64_t)n_total) >> 32) : -1;
+    *lrn = (u01d(x.z) < p.learn_from_rate) ? (int64_t)(((uint64_t)x.w * (uint64_t)n_total) >> 32) : -1;
+}
+
+// Shared tail of both soup modes for one particle (code/soup.py:62-87): learn_from x severity, train x t,
+// cull tests on the OLD particle, respawn keyed by (slot, generation).  Teacher weights (if any) are already
+// in sc.tgt unless teacher_is_self (then samples are re-frozen per call, network.py:623).
+template <class S>
+__device__ __forceinline__ void soup_tail(const SoupP &p, float *cur, const SgdScratch &sc, bool has_teacher,
+                                          bool teacher_is_self, uint64_t seed, uint64_t slot, uint64_t gen,
+                                          const Limits &lim, uint8_t *action, double *loss, float *logged,
+                                          int64_t logged_ld, int64_t logged_i, bool *dead) {
+    const int sev = p.severity > 0 ? p.severity : 0, tr = p.train > 0 ? p.train : 0;
+    const uint64_t ep = gen * (uint64_t)(sev + tr);
+    const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
+    if (has_teacher || teacher_is_self) {
+        for (int e = 0; e < sev; ++e) {
+            if (teacher_is_self) {
+#pragma unroll
+                for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+            }
+            if (ordered) philox_perm<S::NS>(seed, slot, ep + (uint64_t)e, sc.ord, sc.stride);
+            train_epoch<S>(cur, sc, ordered, p.lr);
+        }
+        *action = SRNN_ACT_LEARN;
+    }
+    for (int e = 0; e < tr; ++e) {
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+        if (ordered) philox_perm<S::NS>(seed, slot, ep + (uint64_t)(sev + e), sc.ord, sc.stride);
+        *loss = train_epoch<S>(cur, sc, ordered, p.lr);
+        *action = SRNN_ACT_TRAIN;
+    }
+    if (logged) record_store<S::NW>(logged, logged_ld, logged_i, cur);
+    bool d = false;
+    if (p.remove_divergent && is_diverged<S::NW>(cur)) { d = true; *action = SRNN_ACT_DIV_DEAD; }
+    if (p.remove_zero && is_zero<S::NW>(cur, p.eps.le)) { d = true; *action = SRNN_ACT_ZERO_DEAD; }
+    if (d) init_net<S>(seed, slot, (uint32_t)gen, lim, cur);
+    *dead = d;
+}
+
+// exact order: ONE thread walks the particles in index order (Gauss-Seidel, code/soup.py:54-87)
+template <class S>
+__global__ void soup_ordered_kernel(float *w, int64_t ld, int64_t n, const int64_t *__restrict__ att,
+                                    const int64_t *__restrict__ lrn, SoupP p, uint64_t seed, uint64_t gen,
+                                    Limits lim, uint8_t *action, double *loss, float *logged) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    SgdScratch sc = sgd_scratch<S>(smem, 1);
+    for (int64_t i = 0; i < n; ++i) {
+        float cur[S::NW], oth[S::NW], res[S::NW];
+        uint8_t act = SRNN_ACT_NONE;
+        double ls = nan("");
+        bool dead = false;
+        const float *rec = w + i * ld;
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) cur[k] = rec[k];
+        const int64_t a = att ? att[i] : -1, l = lrn ? lrn[i] : -1;
+        if (a >= 0) {  // particle.attack(other): other <- f_particle(other), soup.py:56-61
+            const float *vr = w + a * ld;
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) oth[k] = vr[k];
+            net_apply<S>(cur, oth, res);
+            record_store<S::NW>(w, ld, a, res);
+            if (a == i) {
+#pragma unroll
+                for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
+            }
+            act = SRNN_ACT_ATTACK;
+        }
+        const bool has_teacher = l >= 0 && l != i, self_teacher = l == i;
+        if (has_teacher) {
+            const float *tr = w + l * ld;
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tr[k];
+        }
+        soup_tail<S>(p, cur, sc, has_teacher, self_teacher, seed, (uint64_t)i, gen, lim, &act, &ls, logged, ld, i, &dead);
+        record_store<S::NW>(w, ld, i, cur);
+        if (action) action[i] = act;
+        if (loss) loss[i] = ls;
+    }
+}
+
+// snapshot-synchronous, phase A: every owner evaluates the same pairing function for ALL global particles and
+// threads the attackers of its local victims into per-victim lists (head[n] | next[n_total]).
+__global__ void __launch_bounds__(BS) soup_lists_kernel(SoupP p, uint64_t seed, uint64_t gen, int64_t n_total,
+                                                        int64_t slot0, int64_t n, int32_t *head, int32_t *next) {
+    const int64_t a = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (a >= n_total) return;
+    int64_t at, lr;
+    soup_draw(p, seed, (uint64_t)a, gen, n_total, &at, &lr);
+    if (at >= slot0 && at < slot0 + n) next[a] = atomicExch(&head[at - slot0], (int32_t)a);
+}
+
+// phase B: the victim's owner thread applies its attackers in ascending index, then learn_from / train / cull.
+template <class S>
+__global__ void __launch_bounds__(BS) soup_sync_kernel(const float *__restrict__ snap, int64_t snap_ld,
+                                                       int64_t n_total, float *__restrict__ w_out, int64_t out_ld,
+                                                       int64_t slot0, int64_t n, SoupP p, uint64_t seed, uint64_t gen,
+                                                       Limits lim, const int32_t *__restrict__ head,
+                                                       const int32_t *__restrict__ next, uint8_t *action,
+                                                       double *loss, uint8_t *dead_out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ float tile[BS * tile_stride<S::NW>()];
+    const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
+    const bool active = i < n;
+    SgdScratch sc = sgd_scratch<S>(smem, BS);
+    float cur[S::NW];
+    tile_load<S::NW>(snap + slot0 * snap_ld, snap_ld, base, n, tile, cur);
+    __syncthreads();
+    if (active) {
+        uint8_t act = SRNN_ACT_NONE;
+        double ls = nan("");
+        bool dead = false;
+        int64_t at, lr;
+        soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at, &lr);
+        if (at >= 0) act = SRNN_ACT_ATTACK;
+        int32_t last = -1;
+        for (;;) {  // lists are short (Poisson(attacking_rate)): select the next-larger attacker by rescanning
+            int32_t best = 0x7fffffff;
+            for (int32_t a = head[i]; a >= 0; a = next[a])
+                if (a > last && a < best) best = a;
+            if (best == 0x7fffffff) break;
+            float op[S::NW], res[S::NW];
+            record_load<S::NW>(snap, snap_ld, best, op);
+            net_apply<S>(op, cur, res);
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
+            last = best;
+        }
+        if (lr >= 0) {
+            const float *tr = snap + lr * snap_ld;
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = __ldg(tr + k);
+        }
+        soup_tail<S>(p, cur, sc, lr >= 0, false, seed, (uint64_t)(slot0 + i), gen, lim, &act, &ls, nullptr, 0, 0, &dead);
+        if (action) action[i] = act;
+        if (loss) loss[i] = ls;
+        if (dead_out) dead_out[i] = dead ? 1 : 0;
+    }
+    tile_store<S::NW>(w_out, out_ld, base, n, tile, cur);
+}
+
+// ================================================================================================ uid scan
+constexpr int SCAN_BS = 1024;
+__global__ void __launch_bounds__(SCAN_BS) uid_count_kernel(const uint8_t *__restrict__ dead, int64_t n, int64_t *block_tmp) {
+    const int64_t i = (int64_t)blockIdx.x * SCAN_BS + threadIdx.x;
+    const int c = __syncthreads_count(i < n && dead[i] != 0);
+    if (threadIdx.x == 0) block_tmp[blockIdx.x] = c;
+}
+__global__ void __launch_bounds__(SCAN_BS) uid_blockscan_kernel(int64_t *block_tmp, int64_t nb, int64_t *n_dead_out) {
+    // exclusive scan of nb block counts by one CTA: each thread owns a contiguous chunk
+    __shared__ int64_t part[SCAN_BS];
+    const int64_t chunk = (nb + SCAN_BS - 1) / SCAN_BS, lo = (int64_t)threadIdx.x * chunk;
+    const int64_t hi = lo + chunk < nb ? lo + chunk : nb;
+    int64_t s = 0;
+    for (int64_t b = lo; b < hi; ++b) s += block_tmp[b];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t run = 0;
+        for (int t = 0; t < SCAN_BS; ++t) { const int64_t v = part[t]; part[t] = run; run += v; }
+        block_tmp[nb] = run;
+        if (n_dead_out) *n_dead_out = run;
+    }
+    __syncthreads();
+    int64_t run = part[threadIdx.x];
+    for (int64_t b = lo; b < hi; ++b) { const int64_t v = block_tmp[b]; block_tmp[b] = run; run += v; }
+}
+__global__ void __launch_bounds__(SCAN_BS) uid_assign_kernel(const uint8_t *__restrict__ dead, int64_t n, int64_t uid_base,
+                                                             const int64_t *__restrict__ block_tmp, int64_t *uid) {
+    __shared__ int warp_tot[SCAN_BS / 32];
+    const int64_t i = (int64_t)blockIdx.x * SCAN_BS + threadIdx.x;
+    const bool d = i < n && dead[i] != 0;
+    const unsigned m = __ballot_sync(0xffffffffu, d);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) warp_tot[wid] = __popc(m);
+    __syncthreads();
+    int before = __popc(m & ((1u << lane) - 1u));
+    for (int q = 0; q < wid; ++q) before += warp_tot[q];
+    if (d) uid[i] = uid_base + block_tmp[blockIdx.x] + before;
+}
+
+// ================================================================================================ FP32 probe
+template <int VARIANT>
+__global__ void __launch_bounds__(BS) fp32_probe_kernel(float *out, int iters) {
+    float acc[16];
+    const float a = 1.0f + 1e-7f * (float)threadIdx.x, b = 1e-9f * (float)blockIdx.x;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) acc[q] = (float)q;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                if constexpr (VARIANT == 0) acc[q] = __fmaf_rn(acc[q], a, b);  // reg, reg, reg
+                else acc[q] = __fmaf_rn(acc[q], 0.99999f, b);                  // reg, imm, reg
+            }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) s += acc[q];
+    out[(int64_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// ================================================================================================ host side
+static Limits make_limits(const srnn_net_desc *d) {
+    Limits lim;
+    const int nl = d->depth + 1;
+    const int io = d->kind == SRNN_KIND_WW ? 4 : (d->kind == SRNN_KIND_AGG ? d->aggregates : 1);
+    for (int l = 0; l < SRNN_MAX_LAYERS; ++l) {
+        const int in = l == 0 ? io : d->width;
+        const int out = l == nl - 1 ? (d->kind == SRNN_KIND_WW ? 1 : io) : d->width;
+        lim.v[l] = (float)sqrt(6.0 / (double)(in + out));
+    }
+    return lim;
+}
+static int make_soup(const srnn_soup_params *p, SoupP *q) {
+    if (!p) return fail(SRNN_ERR_ARG, "soup params is NULL%s");
+    q->attacking_rate = p->attacking_rate;
+    q->learn_from_rate = p->learn_from_rate;
+    q->train = p->train;
+    q->severity = p->learn_from_severity;
+    q->remove_divergent = p->remove_divergent;
+    q->remove_zero = p->remove_zero;
+    q->perm_mode = p->perm_mode;
+    q->lr = p->lr;
+    if (p->perm_mode != SRNN_PERM_NONE && p->perm_mode != SRNN_PERM_PHILOX)
+        return fail(SRNN_ERR_ARG, "soup perm_mode must be SRNN_PERM_NONE or SRNN_PERM_PHILOX%s");
+    return make_eps(p->epsilon, &q->eps);
+}
+
+// the instantiated net shapes: (kind, width, depth, aggregates)
+#define SRNN_SHAPES(X)                                                                               \
+    X(SRNN_KIND_WW, 2, 2, 0) X(SRNN_KIND_WW, 3, 2, 0) X(SRNN_KIND_WW, 2, 3, 0) X(SRNN_KIND_WW, 2, 1, 0) \
+    X(SRNN_KIND_AGG, 2, 2, 4) X(SRNN_KIND_AGG, 2, 2, 3) X(SRNN_KIND_AGG, 3, 2, 4)                    \
+    X(SRNN_KIND_RNN, 2, 2, 0) X(SRNN_KIND_RNN, 2, 1, 0)
+
+static inline long shape_key(int kind, int width, int depth, int aggs) {
+    return ((long)kind << 24) | ((long)width << 16) | ((long)depth << 8) | (long)(kind == SRNN_KIND_AGG ? aggs : 0);
+}
+#define SRNN_CASE(KIND, W, D, A)                    \
+    case ((long)(KIND) << 24) | ((long)(W) << 16) | ((long)(D) << 8) | (long)(A): { \
+        using S = Shape<KIND, W, D, A>;             \
+        BODY(S)                                     \
+    } break;
+#define SRNN_DISPATCH(d)                                                                              \
+    switch (shape_key((d)->kind, (d)->width, (d)->depth, (d)->aggregates)) {                          \
+        SRNN_SHAPES(SRNN_CASE)                                                                        \
+        default: return fail(SRNN_ERR_SHAPE, "net shape not instantiated in libsrnn_b200 (see SRNN_SHAPES)%s"); \
+    }
+
+static inline unsigned grid_for(int64_t n) { return (unsigned)((n + BS - 1) / BS); }
+
+template <class K>
+static int allow_smem(K kernel, size_t bytes) {
+    if (bytes > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (e != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
+    return SRNN_OK;
+}
+
+}  // namespace srnn
+
+using namespace srnn;
+
+extern "C" {
+
+int srnn_version(void) { return 100; }
+const char *srnn_last_error_string(void) { return g_err; }
+
+int srnn_set_device(int device) {
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    return SRNN_OK;
+}
+
+int srnn_desc_init(srnn_net_desc *d) {
+    if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
+    if (d->width < 1 || d->width > SRNN_MAX_WIDTH || d->depth < 1 || d->depth + 1 > SRNN_MAX_LAYERS)
+        return fail(SRNN_ERR_SHAPE, "width/depth out of range%s");
+    int io;
+    if (d->kind == SRNN_KIND_WW) io = 4;
+    else if (d->kind == SRNN_KIND_AGG) io = d->aggregates;
+    else if (d->kind == SRNN_KIND_RNN) io = 1;
+    else return fail(SRNN_ERR_SHAPE, "unknown net kind%s");
+    if (io < 1 || io > SRNN_MAX_WIDTH) return fail(SRNN_ERR_SHAPE, "aggregates out of range%s");
+    int off = 0;
+    for (int l = 0; l <= d->depth; ++l) {
+        const int in = l == 0 ? io : d->width;
+        const int out = l == d->depth ? (d->kind == SRNN_KIND_WW ? 1 : io) : d->width;
+        off += in * out + (d->kind == SRNN_KIND_RNN ? out * out : 0);
+    }
+    if (off > SRNN_MAX_WEIGHTS) return fail(SRNN_ERR_LIMIT, "more than SRNN_MAX_WEIGHTS weights%s");
+    if (d->kind == SRNN_KIND_AGG) {
+        const int cs = off / io;
+        if (cs < 1 || off - cs * io >= cs)
+            return fail(SRNN_ERR_SHAPE, "aggregating shape whose leftovers fill another collection (reference raises)%s");
+    }
+    d->n_weights = off;
+    return SRNN_OK;
+}
+
+int srnn_shape_supported(const srnn_net_desc *d) {
+    if (!d) return 0;
+#define BODY(S) return 1;
+    switch (shape_key(d->kind, d->width, d->depth, d->aggregates)) {
+        SRNN_SHAPES(SRNN_CASE)
+        default: return 0;
+    }
+#undef BODY
+}
+
+#define SRNN_CHECK_ARENA(w, ld, S)                                                              \
+    if (!(w)) return fail(SRNN_ERR_ARG, "arena pointer is NULL%s");                              \
+    if ((ld) < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");
+
+int srnn_apply(const srnn_net_desc *d, const float *op_w, int64_t op_ld, const int32_t *op_idx, const float *in_w,
+               int64_t in_ld, const int32_t *in_idx, float *out_w, int64_t out_ld, const int32_t *out_idx, int64_t n,
+               void *stream) {
+    if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+#define BODY(S)                                                                                              \
+    SRNN_CHECK_ARENA(op_w, op_ld, S) SRNN_CHECK_ARENA(in_w, in_ld, S) SRNN_CHECK_ARENA(out_w, out_ld, S)     \
+    apply_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(op_w, op_ld, op_idx, in_w, in_ld, in_idx, out_w, \
+                                                                  out_ld, out_idx, n);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_apply");
+}
+
+int srnn_self_apply(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t n_steps, int32_t mode, double eps,
+                    int32_t with_fix_sec, int32_t *steps_out, uint8_t *cls_out, int64_t *counters, float *traj,
+                    void *stream) {
+    if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    if (n_steps < 0) return fail(SRNN_ERR_ARG, "n_steps < 0%s");
+    if (mode != SRNN_RUN_FIXED && mode != SRNN_RUN_UNTIL) return fail(SRNN_ERR_ARG, "unknown run mode%s");
+    const bool fast = mode == SRNN_RUN_FIXED && !steps_out && !cls_out && !counters && !traj;
+    Eps e{0.f, 0.f};
+    if (!fast) { int rc = make_eps(eps, &e); if (rc) return rc; }
+#define BODY(S)                                                                                              \
+    SRNN_CHECK_ARENA(w, ld, S)                                                                               \
+    if (fast) self_apply_fixed_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, n, n_steps);   \
+    else self_apply_general_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(                         \
+            w, ld, n, n_steps, mode, e, with_fix_sec, steps_out, cls_out, (unsigned long long *)counters, traj);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_self_apply");
+}
+
+int srnn_classify(const srnn_net_desc *d, const float *w, int64_t ld, int64_t n, double eps, int32_t with_fix_sec,
+                  uint8_t *cls_out, uint8_t *flags_out, int64_t *counters, void *stream) {
+    if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    Eps e;
+    int rc = make_eps(eps, &e);
+    if (rc) return rc;
+#define BODY(S)                                                                                              \
+    SRNN_CHECK_ARENA(w, ld, S)                                                                               \
+    classify_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, n, e, with_fix_sec, cls_out, flags_out, \
+                                                                     (unsigned long long *)counters);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_classify");
+}
+
+int srnn_train(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t n_epochs, float lr, int32_t perm_mode,
+               const uint8_t *perm, uint64_t seed, uint64_t slot0, uint64_t epoch0, const float *teacher_w,
+               int64_t teacher_ld, const int32_t *teacher_idx, double *loss_out, void *stream) {
+    if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    if (n_epochs < 0) return fail(SRNN_ERR_ARG, "n_epochs < 0%s");
+    if (perm_mode < SRNN_PERM_NONE || perm_mode > SRNN_PERM_PHILOX) return fail(SRNN_ERR_ARG, "unknown perm_mode%s");
+    if (perm_mode == SRNN_PERM_EXPLICIT && !perm) return fail(SRNN_ERR_ARG, "SRNN_PERM_EXPLICIT needs perm%s");
+#define BODY(S)                                                                                              \
+    SRNN_CHECK_ARENA(w, ld, S)                                                                               \
+    if (teacher_w && teacher_ld < S::NW) return fail(SRNN_ERR_ARG, "teacher_ld is smaller than n_weights%s"); \
+    const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
+    int rc = allow_smem(train_kernel<S>, sm + sizeof(float) * BS * tile_stride<S::NW>());                    \
+    if (rc) return rc;                                                                                       \
+    train_kernel<S><<<grid_for(n), BS, sm, (cudaStream_t)stream>>>(w, ld, n, n_epochs, lr, perm_mode, perm, seed, slot0, \
+                                                                   epoch0, teacher_w, teacher_ld, teacher_idx, loss_out);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_train");
+}
+
+int srnn_init(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, const int32_t *idx, uint64_t seed,
+              uint64_t slot0, uint32_t generation, void *stream) {
+    if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    const Limits lim = make_limits(d);
+#define BODY(S)                \
+    SRNN_CHECK_ARENA(w, ld, S) \
+    init_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, n, idx, seed, slot0, generation, lim);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_init");
+}
+
+int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double scale, uint32_t level, int32_t max_steps,
+             double eps, uint64_t seed, uint64_t slot0, int32_t *time_to_vergence, int32_t *time_as_fixpoint,
+             int64_t *hist, float *w_out, int64_t ld, void *stream) {
+    if (!d || !base_host) return fail(SRNN_ERR_ARG, "desc or base is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    if (max_steps < 0) return fail(SRNN_ERR_ARG, "max_steps < 0%s");
+    Eps e;
+    int rc = make_eps(eps, &e);
+    if (rc) return rc;
+    BaseNet bn;
+    memset(&bn, 0, sizeof bn);
+#define BODY(S)                                                                                              \
+    if (w_out && ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");       \
+    memcpy(bn.v, base_host, sizeof(float) * S::NW);                                                          \
+    kfv_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(bn, n, scale, level, max_steps, e, seed, slot0, \
+                                                                time_to_vergence, time_as_fixpoint,           \
+                                                                (unsigned long long *)hist, w_out, ld);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_kfv");
+}
+
+int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n,
+                      const int64_t *att, const int64_t *lrn, uint64_t seed, uint64_t gen, uint8_t *action,
+                      double *loss, float *logged, void *stream) {
+    if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    SoupP q;
+    int rc = make_soup(p, &q);
+    if (rc) return rc;
+    const Limits lim = make_limits(d);
+#define BODY(S)                                                                                              \
+    SRNN_CHECK_ARENA(w, ld, S)                                                                               \
+    soup_ordered_kernel<S><<<1, 32, sgd_smem_bytes<S>(1), (cudaStream_t)stream>>>(w, ld, n, att, lrn, q, seed, gen, lim, \
+                                                                                  action, loss, logged);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_soup_ordered");
+}
+
+int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const float *snap, int64_t snap_ld,
+                   int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed, uint64_t gen,
+                   int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream) {
+    if (!d || !scratch) return fail(SRNN_ERR_ARG, "desc or scratch is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    if (n_total >= 0x7fffffffLL || slot0 < 0 || slot0 + n > n_total)
+        return fail(SRNN_ERR_ARG, "need 0 <= slot0, slot0 + n <= n_total < 2^31%s");
+    if ((const float *)w_out == snap) return fail(SRNN_ERR_ARG, "w_out must not alias snap%s");
+    SoupP q;
+    int rc = make_soup(p, &q);
+    if (rc) return rc;
+    const Limits lim = make_limits(d);
+    int32_t *head = scratch, *next = scratch + n;
+    cudaError_t ce = cudaMemsetAsync(head, 0xFF, sizeof(int32_t) * (size_t)n, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    if (q.attacking_rate > 0.0)
+        soup_lists_kernel<<<grid_for(n_total), BS, 0, (cudaStream_t)stream>>>(q, seed, gen, n_total, slot0, n, head, next);
+#define BODY(S)                                                                                              \
+    SRNN_CHECK_ARENA(snap, snap_ld, S) SRNN_CHECK_ARENA(w_out, out_ld, S)                                    \
+    const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
+    rc = allow_smem(soup_sync_kernel<S>, sm + sizeof(float) * BS * tile_stride<S::NW>());                    \
+    if (rc) return rc;                                                                                       \
+    soup_sync_kernel<S><<<grid_for(n), BS, sm, (cudaStream_t)stream>>>(snap, snap_ld, n_total, w_out, out_ld, slot0, n, q, \
+                                                                       seed, gen, lim, head, next, action, loss, dead);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_soup_sync");
+}
+
+int srnn_assign_uids(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *uid, int64_t *block_tmp,
+                     int64_t *n_dead_out, void *stream) {
+    if (!dead || !uid || !block_tmp) return fail(SRNN_ERR_ARG, "dead, uid or block_tmp is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    const int64_t nb = (n + SCAN_BS - 1) / SCAN_BS;
+    uid_count_kernel<<<(unsigned)nb, SCAN_BS, 0, (cudaStream_t)stream>>>(dead, n, block_tmp);
+    uid_blockscan_kernel<<<1, SCAN_BS, 0, (cudaStream_t)stream>>>(block_tmp, nb, n_dead_out);
+    uid_assign_kernel<<<(unsigned)nb, SCAN_BS, 0, (cudaStream_t)stream>>>(dead, n, uid_base, block_tmp, uid);
+    return check_launch("srnn_assign_uids");
+}
+
+int srnn_fp32_probe(float *out, int32_t grid, int32_t block, int32_t iters, void *stream) {
+    if (!out || grid < 1 || block < 1 || block > BS) return fail(SRNN_ERR_ARG, "bad probe arguments%s");
+    if (iters >= 0) fp32_probe_kernel<0><<<grid, block, 0, (cudaStream_t)stream>>>(out, iters);
+    else fp32_probe_kernel<1><<<grid, block, 0, (cudaStream_t)stream>>>(out, -iters);
+    return check_launch("srnn_fp32_probe");
+}
+
+}  // extern "C"

@@ -1,0 +1,498 @@
+// srnn_device.cuh -- device-side building blocks of libsrnn_b200.so (sm_100a).
+//
+// Everything a single net needs is held in registers by ONE thread: its weight record (14 / 20 / 17
+// floats for the benchmarked shapes), the operator's temporaries and, for SGD, the activations.  Net
+// shapes are compile-time (template Shape<>) so every weight index is a constant after unrolling and
+// the position codes of the weightwise net become FFMA immediates.
+//
+// Arithmetic is pinned to the reference's committed Keras trajectories (DESIGN.md "Pinned arithmetic"):
+// compile with -fmad=false -ftz=true -prec-div=true -prec-sqrt=true and spell every fusion explicitly.
+//   R2  Dense, >= 2 output units:  acc = rn(x0*W0j); acc = fma(xk, Wkj, acc), k ascending
+//   R3  Dense, 1 output unit:      acc = +0; acc = rn(acc + rn(xk*Wk)), k ascending
+//   R4  position codes = (float)((double)i / (double)max)
+//   R5  AGG block mean = f64 sequential sum / count, cast to f32
+//   R6  predicates on f32 values against f32-rounded epsilons (host rounds eps up / down, see srnn_b200.cu)
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <type_traits>
+#include <utility>
+
+#include "../../include/srnn_types.h"
+
+namespace srnn {
+
+#define SRNN_DEV __device__ __forceinline__
+#define SRNN_HD __host__ __device__ constexpr
+
+template <int I, int N, class F>
+SRNN_DEV void static_for(F &&f) {
+    if constexpr (I < N) {
+        f(std::integral_constant<int, I>{});
+        static_for<I + 1, N>(f);
+    }
+}
+// counts down: I = N-1 .. 0
+template <int N, class F>
+SRNN_DEV void static_rfor(F &&f) {
+    if constexpr (N > 0) {
+        f(std::integral_constant<int, N - 1>{});
+        static_rfor<N - 1>(f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ shapes
+// Keras layer stacks of code/network.py:226-230 (WW: 4 -> width x depth -> 1), :329-333 (AGG: a -> ... -> a),
+// :531-535 (RNN: SimpleRNN 1 -> width x depth -> 1, each with input kernel K and recurrent kernel U).
+template <int KIND_, int WIDTH_, int DEPTH_, int AGG_>
+struct ShapeFn {  // helpers live in a base so they are complete when Shape's constants are evaluated
+    static constexpr int NL = DEPTH_ + 1;
+    static constexpr int IO = KIND_ == SRNN_KIND_WW ? 4 : (KIND_ == SRNN_KIND_AGG ? AGG_ : 1);
+    static constexpr int OUTW = KIND_ == SRNN_KIND_WW ? 1 : IO;
+    static SRNN_HD int in(int l) { return l == 0 ? IO : WIDTH_; }
+    static SRNN_HD int out(int l) { return l == NL - 1 ? OUTW : WIDTH_; }
+    static SRNN_HD int layer_size(int l) { return in(l) * out(l) + (KIND_ == SRNN_KIND_RNN ? out(l) * out(l) : 0); }
+    static SRNN_HD int off(int l) {
+        int o = 0;
+        for (int q = 0; q < l; ++q) o += layer_size(q);
+        return o;
+    }
+    static SRNN_HD int offU(int l) { return off(l) + in(l) * out(l); }
+    // weightwise position codes: compute_all_duplex_weight_points, code/network.py:239-255 (rule R4)
+    static SRNN_HD int layer_of(int k) {
+        int l = 0;
+        while (l < NL - 1 && k >= off(l + 1)) ++l;
+        return l;
+    }
+    static SRNN_HD float norm_id(int v, int mx) { return (float)(mx > 1 ? (double)v / (double)mx : (double)v); }
+    static SRNN_HD float codeL(int k) { return norm_id(layer_of(k), NL - 1); }
+    static SRNN_HD float codeR(int k) { return norm_id((k - off(layer_of(k))) / out(layer_of(k)), in(layer_of(k)) - 1); }
+    static SRNN_HD float codeC(int k) { return norm_id((k - off(layer_of(k))) % out(layer_of(k)), out(layer_of(k)) - 1); }
+};
+template <int KIND_, int WIDTH_, int DEPTH_, int AGG_>
+struct Shape : ShapeFn<KIND_, WIDTH_, DEPTH_, AGG_> {
+    using Fn = ShapeFn<KIND_, WIDTH_, DEPTH_, AGG_>;
+    static constexpr int KIND = KIND_, WIDTH = WIDTH_, DEPTH = DEPTH_, AGGS = AGG_;
+    static constexpr int NL = Fn::NL, IO = Fn::IO, OUTW = Fn::OUTW;
+    static constexpr int MAXU = IO > WIDTH_ ? IO : WIDTH_;
+    static constexpr int NW = Fn::off(NL);
+    static constexpr int NS = KIND_ == SRNN_KIND_WW ? NW : 1;  // SGD samples per epoch
+    // aggregating net: collect_weights, code/network.py:388-403 -- block g = [g*CS, (g+1)*CS), last takes the rest
+    static constexpr int CS = KIND_ == SRNN_KIND_AGG ? NW / (AGG_ > 0 ? AGG_ : 1) : 0;
+};
+
+// ------------------------------------------------------------------------------------------------ dense
+template <int IN, int OUT>
+SRNN_DEV void dense(const float *x, const float *W, float *y) {
+    if constexpr (OUT >= 2) {  // R2
+#pragma unroll
+        for (int j = 0; j < OUT; ++j) {
+            float acc = __fmul_rn(x[0], W[j]);
+#pragma unroll
+            for (int k = 1; k < IN; ++k) acc = __fmaf_rn(x[k], W[k * OUT + j], acc);
+            y[j] = acc;
+        }
+    } else {  // R3
+        float acc = 0.0f;
+#pragma unroll
+        for (int k = 0; k < IN; ++k) acc = __fadd_rn(acc, __fmul_rn(x[k], W[k]));
+        y[0] = acc;
+    }
+}
+// gp[i] = sum_j g[j] * W[i][j]   (backward of Dense; same rules keyed on the IN result units)
+template <int IN, int OUT>
+SRNN_DEV void dense_T(const float *g, const float *W, float *gp) {
+    if constexpr (IN >= 2) {
+#pragma unroll
+        for (int i = 0; i < IN; ++i) {
+            float acc = __fmul_rn(g[0], W[i * OUT]);
+#pragma unroll
+            for (int j = 1; j < OUT; ++j) acc = __fmaf_rn(g[j], W[i * OUT + j], acc);
+            gp[i] = acc;
+        }
+    } else {
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < OUT; ++j) acc = __fadd_rn(acc, __fmul_rn(g[j], W[j]));
+        gp[0] = acc;
+    }
+}
+
+template <class S, int L = 0>
+SRNN_DEV void mlp_forward(const float *w, const float *x, float *y) {
+    if constexpr (L == S::NL - 1) {
+        dense<S::in(L), S::out(L)>(x, w + S::off(L), y);
+    } else {
+        float h[S::MAXU];
+        dense<S::in(L), S::out(L)>(x, w + S::off(L), h);
+        mlp_forward<S, L + 1>(w, h, y);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ operators
+// out <- f_op(in);  `out` must not alias `in` or `op`.
+// WeightwiseNeuralNetwork.apply_to_weights, code/network.py:265-279
+template <class S>
+SRNN_DEV void ww_apply(const float *op, const float *in, float *out) {
+    static_for<0, S::NW>([&](auto K) {
+        constexpr int k = decltype(K)::value;
+        const float x[4] = {in[k], S::codeL(k), S::codeR(k), S::codeC(k)};
+        mlp_forward<S>(op, x, &out[k]);
+    });
+}
+// AggregatingNeuralNetwork.apply_to_weights, code/network.py:359-386 (aggregate_average :294-301, R5)
+template <class S>
+SRNN_DEV void agg_means(const float *in, float *agg) {
+    static_for<0, S::AGGS>([&](auto G) {
+        constexpr int g = decltype(G)::value;
+        constexpr int lo = g * S::CS, hi = g == S::AGGS - 1 ? S::NW : lo + S::CS;
+        double tot = 0.0;
+#pragma unroll
+        for (int k = lo; k < hi; ++k) tot = __dadd_rn(tot, (double)in[k]);
+        agg[g] = (float)__ddiv_rn(tot, (double)(hi - lo));
+    });
+}
+template <class S>
+SRNN_DEV void agg_apply(const float *op, const float *in, float *out) {
+    float agg[S::AGGS > 0 ? S::AGGS : 1], res[S::AGGS > 0 ? S::AGGS : 1];
+    agg_means<S>(in, agg);
+    mlp_forward<S>(op, agg, res);
+    static_for<0, S::AGGS>([&](auto G) {
+        constexpr int g = decltype(G)::value;
+        constexpr int lo = g * S::CS, hi = g == S::AGGS - 1 ? S::NW : lo + S::CS;
+#pragma unroll
+        for (int k = lo; k < hi; ++k) out[k] = res[g];
+    });
+}
+// RecurrentNeuralNetwork.apply_to_weights, code/network.py:544-564: h_t = rn(dense(x_t, K) + dense(h_{t-1}, U)),
+// h_{-1} = 0, layers chained per time step.  HIST = true also records every h (for BPTT): hist[(l*T + t)*MAXU + j].
+template <class S, bool HIST>
+SRNN_DEV void rnn_forward_seq(const float *op, const float *seq, float *out, float *hist) {
+    constexpr int T = S::NW;
+    float h[S::NL][S::MAXU];
+#pragma unroll
+    for (int l = 0; l < S::NL; ++l)
+#pragma unroll
+        for (int j = 0; j < S::MAXU; ++j) h[l][j] = 0.0f;
+    static_for<0, T>([&](auto TT) {
+        constexpr int t = decltype(TT)::value;
+        float x[S::MAXU];
+        x[0] = seq[t];
+        static_for<0, S::NL>([&](auto LL) {
+            constexpr int l = decltype(LL)::value;
+            float a[S::MAXU], b[S::MAXU];
+            dense<S::in(l), S::out(l)>(x, op + S::off(l), a);
+            dense<S::out(l), S::out(l)>(h[l], op + S::offU(l), b);
+#pragma unroll
+            for (int j = 0; j < S::out(l); ++j) {
+                h[l][j] = __fadd_rn(a[j], b[j]);
+                x[j] = h[l][j];
+                if constexpr (HIST) hist[(l * T + t) * S::MAXU + j] = h[l][j];
+            }
+        });
+        out[t] = x[0];
+    });
+}
+template <class S>
+SRNN_DEV void net_apply(const float *op, const float *in, float *out) {
+    if constexpr (S::KIND == SRNN_KIND_WW) ww_apply<S>(op, in, out);
+    else if constexpr (S::KIND == SRNN_KIND_AGG) agg_apply<S>(op, in, out);
+    else rnn_forward_seq<S, false>(op, in, out, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------------ predicates
+// are_weights_diverged, code/network.py:43-52
+template <int N>
+SRNN_DEV bool is_diverged(const float *w) {
+    bool d = false;
+#pragma unroll
+    for (int k = 0; k < N; ++k) d |= !(fabsf(w[k]) <= 3.402823466e+38f);
+    return d;
+}
+// is_zero, code/network.py:136-138: all -eps <= w <= eps  (eps_le = largest f32 <= eps)
+template <int N>
+SRNN_DEV bool is_zero(const float *w, float eps_le) {
+    bool z = true;
+#pragma unroll
+    for (int k = 0; k < N; ++k) z &= (fabsf(w[k]) <= eps_le);
+    return z;
+}
+// tail of is_fixpoint, code/network.py:149-157: nw = iterated application result (eps_ge = smallest f32 >= eps)
+template <int N>
+SRNN_DEV bool is_close(const float *nw, const float *w, float eps_ge) {
+    bool ok = !is_diverged<N>(nw);
+#pragma unroll
+    for (int k = 0; k < N; ++k) ok &= !(fabsf(__fsub_rn(nw[k], w[k])) >= eps_ge);
+    return ok;
+}
+// decision list of FixpointExperiment.count, code/experiment.py:79-91; nw = f_w(w) already known
+template <class S>
+SRNN_DEV int classify_with(const float *w, const float *nw, float eps_ge, float eps_le, int with_fix_sec) {
+    if (is_diverged<S::NW>(w)) return SRNN_CLS_DIVERGENT;
+    if (is_close<S::NW>(nw, w, eps_ge)) return is_zero<S::NW>(w, eps_le) ? SRNN_CLS_FIX_ZERO : SRNN_CLS_FIX_OTHER;
+    if (with_fix_sec) {
+        float nnw[S::NW];
+        net_apply<S>(w, nw, nnw);  // is_fixpoint(2): the operator stays at w
+        if (is_close<S::NW>(nnw, w, eps_ge)) return SRNN_CLS_FIX_SEC;
+    }
+    return SRNN_CLS_OTHER;
+}
+
+// ------------------------------------------------------------------------------------------------ Philox4x32-10
+struct U4 { uint32_t x, y, z, w; };
+SRNN_DEV U4 philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return U4{c0, c1, c2, c3};
+}
+// streams: counter = (slot_lo, slot_hi(24b) | stream << 24, a, b), key = seed.  slot = GLOBAL net index.
+enum { ST_INIT = 1, ST_PERM = 2, ST_SOUP = 3, ST_KFV = 4, ST_ORTHO = 5 };
+SRNN_DEV U4 rng4(uint64_t seed, int stream, uint64_t slot, uint32_t a, uint32_t b) {
+    return philox4x32((uint32_t)slot, (uint32_t)((slot >> 32) & 0xFFFFFFu) | ((uint32_t)stream << 24), a, b,
+                      (uint32_t)seed, (uint32_t)(seed >> 32));
+}
+SRNN_DEV uint32_t word_of(const U4 &v, int q) { return q == 0 ? v.x : (q == 1 ? v.y : (q == 2 ? v.z : v.w)); }
+SRNN_DEV float u01f(uint32_t x) { return __fmul_rn((float)(x >> 8), 5.9604644775390625e-08f); }
+SRNN_DEV double u01d(uint32_t x) { return __dmul_rn((double)x, 2.3283064365386963e-10); }
+
+// ------------------------------------------------------------------------------------------------ init / respawn
+// glorot_uniform kernels + orthogonal recurrent kernels (Gram-Schmidt of rejection-sampled unit-ball rows);
+// only + - * / sqrt, so it matches the oracle bit-for-bit.  limits[l] = (float)sqrt(6/(in+out)) from the host.
+template <class S>
+SRNN_DEV void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, float *U) {
+    constexpr int NMAX = S::MAXU;
+    const int n = layer == S::NL - 1 ? S::OUTW : S::WIDTH;
+    uint32_t blk = 0;
+    for (int r = 0; r < n; ++r) {
+        for (int attempt = 0; attempt < 64; ++attempt) {
+            float v[NMAX];
+            for (int c = 0; c < n; c += 4) {
+                const U4 x = rng4(seed, ST_ORTHO, slot, gen, ((uint32_t)layer << 24) | blk++);
+                for (int q = 0; q < 4 && c + q < n; ++q)
+                    v[c + q] = __fsub_rn(__fmul_rn(2.0f, u01f(word_of(x, q))), 1.0f);
+            }
+            float nn = 0.f;
+            for (int c = 0; c < n; ++c) nn = __fadd_rn(nn, __fmul_rn(v[c], v[c]));
+            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; break; }  // 1x1 orthogonal = +-1 exactly
+            if (nn > 1.0f || nn < 1e-4f) continue;
+            for (int p = 0; p < r; ++p) {
+                float dot = 0.f;
+                for (int c = 0; c < n; ++c) dot = __fadd_rn(dot, __fmul_rn(v[c], U[p * n + c]));
+                for (int c = 0; c < n; ++c) v[c] = __fsub_rn(v[c], __fmul_rn(dot, U[p * n + c]));
+            }
+            nn = 0.f;
+            for (int c = 0; c < n; ++c) nn = __fadd_rn(nn, __fmul_rn(v[c], v[c]));
+            if (nn < 1e-2f) continue;
+            const float inv = __fdiv_rn(1.0f, __fsqrt_rn(nn));
+            for (int c = 0; c < n; ++c) U[r * n + c] = __fmul_rn(v[c], inv);
+            break;
+        }
+    }
+}
+struct Limits { float v[SRNN_MAX_LAYERS]; };
+template <class S>
+SRNN_DEV void init_net(uint64_t seed, uint64_t slot, uint32_t gen, const Limits &lim, float *w) {
+    static_for<0, S::NL>([&](auto LL) {
+        constexpr int l = decltype(LL)::value;
+        const float limit = lim.v[l];
+#pragma unroll
+        for (int q = 0; q < S::in(l) * S::out(l); ++q) {
+            const int k = S::off(l) + q;
+            const U4 x = rng4(seed, ST_INIT, slot, gen, (uint32_t)(k >> 2));
+            w[k] = __fmul_rn(__fsub_rn(__fmul_rn(2.0f, u01f(word_of(x, k & 3))), 1.0f), limit);
+        }
+        if constexpr (S::KIND == SRNN_KIND_RNN) {
+            float U[S::MAXU * S::MAXU];
+            ortho_rows<S>(seed, slot, gen, l, U);
+#pragma unroll
+            for (int q = 0; q < S::out(l) * S::out(l); ++q) w[S::offU(l) + q] = U[q];
+        }
+    });
+}
+
+// ------------------------------------------------------------------------------------------------ SGD
+// One sample of Keras SGD(lr) on MSE, batch 1 (TrainingNeuralNetworkDecorator.train / learn_from,
+// code/network.py:613-626): forward, g = (1/n_out) * 2 (out - y), per layer dW = act^T g (single products),
+// g_prev = dense_T(g, W) with the PRE-update W, then W <- rn(W - rn(lr * dW)).  Returns the f32 sample loss.
+template <class S>
+SRNN_DEV float mlp_sgd_sample(float *w, const float *x, const float *y, float lr) {
+    float act[S::NL + 1][S::MAXU];
+#pragma unroll
+    for (int i = 0; i < S::IO; ++i) act[0][i] = x[i];
+    static_for<0, S::NL>([&](auto LL) {
+        constexpr int l = decltype(LL)::value;
+        dense<S::in(l), S::out(l)>(act[l], w + S::off(l), act[l + 1]);
+    });
+    constexpr int NO = S::OUTW;
+    float g[S::MAXU];
+    const float inv = __fdiv_rn(1.0f, (float)NO);
+    float tot = 0.f;
+#pragma unroll
+    for (int j = 0; j < NO; ++j) {
+        const float dlt = __fsub_rn(act[S::NL][j], y[j]);
+        tot = __fadd_rn(tot, __fmul_rn(dlt, dlt));
+        g[j] = __fmul_rn(inv, __fmul_rn(2.0f, dlt));
+    }
+    const float loss = __fdiv_rn(tot, (float)NO);
+    static_rfor<S::NL>([&](auto LL) {
+        constexpr int l = decltype(LL)::value;
+        constexpr int IN = S::in(l), OUT = S::out(l);
+        float *W = w + S::off(l);
+        float gp[S::MAXU];
+        if constexpr (l > 0) dense_T<IN, OUT>(g, W, gp);
+#pragma unroll
+        for (int i = 0; i < IN; ++i)
+#pragma unroll
+            for (int j = 0; j < OUT; ++j)
+                W[i * OUT + j] = __fsub_rn(W[i * OUT + j], __fmul_rn(lr, __fmul_rn(act[l][i], g[j])));
+        if constexpr (l > 0) {
+#pragma unroll
+            for (int i = 0; i < IN; ++i) g[i] = gp[i];
+        }
+    });
+    return loss;
+}
+
+// BPTT through the stacked linear SimpleRNN; one sample = the whole weight sequence (compute_samples,
+// code/network.py:566-574); loss = mean_t (out_t - y_t)^2; contributions accumulated for t descending.
+template <class S>
+SRNN_DEV float rnn_sgd_sample(float *w, const float *seq, float lr) {
+    constexpr int T = S::NW;
+    float hist[S::NL * T * S::MAXU];
+    float out[T];
+    rnn_forward_seq<S, true>(w, seq, out, hist);
+    float dW[S::NW];
+#pragma unroll
+    for (int k = 0; k < S::NW; ++k) dW[k] = 0.f;
+    float dh_next[S::NL][S::MAXU];
+#pragma unroll
+    for (int l = 0; l < S::NL; ++l)
+#pragma unroll
+        for (int j = 0; j < S::MAXU; ++j) dh_next[l][j] = 0.f;
+    const float inv = __fdiv_rn(1.0f, (float)T);
+    float tot = 0.f;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        const float dlt = __fsub_rn(out[t], seq[t]);
+        tot = __fadd_rn(tot, __fmul_rn(dlt, dlt));
+    }
+    const float loss = __fdiv_rn(tot, (float)T);
+    static_rfor<T>([&](auto TT) {
+        constexpr int t = decltype(TT)::value;
+        float dx[S::MAXU];
+        dx[0] = __fmul_rn(inv, __fmul_rn(2.0f, __fsub_rn(out[t], seq[t])));
+        static_rfor<S::NL>([&](auto LL) {
+            constexpr int l = decltype(LL)::value;
+            constexpr int u = S::out(l), in = S::in(l);
+            const float *K = w + S::off(l), *U = w + S::offU(l);
+            float dh[S::MAXU], rec[S::MAXU];
+            dense_T<u, u>(dh_next[l], U, rec);
+#pragma unroll
+            for (int j = 0; j < u; ++j) dh[j] = __fadd_rn(dx[j], rec[j]);
+#pragma unroll
+            for (int i = 0; i < in; ++i) {
+                float xi;
+                if constexpr (l == 0) xi = seq[t];
+                else xi = hist[((l - 1) * T + t) * S::MAXU + i];
+#pragma unroll
+                for (int j = 0; j < u; ++j)
+                    dW[S::off(l) + i * u + j] = __fadd_rn(dW[S::off(l) + i * u + j], __fmul_rn(xi, dh[j]));
+            }
+            if constexpr (t > 0) {
+#pragma unroll
+                for (int i = 0; i < u; ++i)
+#pragma unroll
+                    for (int j = 0; j < u; ++j)
+                        dW[S::offU(l) + i * u + j] = __fadd_rn(dW[S::offU(l) + i * u + j],
+                                                               __fmul_rn(hist[(l * T + t - 1) * S::MAXU + i], dh[j]));
+            }
+            if constexpr (l > 0) {
+                float dxin[S::MAXU];
+                dense_T<in, u>(dh, K, dxin);
+#pragma unroll
+                for (int i = 0; i < in; ++i) dx[i] = dxin[i];
+            }
+#pragma unroll
+            for (int j = 0; j < u; ++j) dh_next[l][j] = dh[j];
+        });
+    });
+#pragma unroll
+    for (int k = 0; k < S::NW; ++k) w[k] = __fsub_rn(w[k], __fmul_rn(lr, dW[k]));
+    return loss;
+}
+
+// Per-thread SGD scratch in shared memory, one column per thread (conflict-free: address = row*stride + tid):
+//   tgt[k]   frozen sample source (the teacher's weights, or a copy of the net's own weights)   NW rows
+//   ord[q]   sample order of the current epoch                                                  NS rows (bytes)
+struct SgdScratch {
+    float *tgt;
+    uint8_t *ord;
+    int stride;       // threads per block (column stride)
+    const float *codes;  // WW: [3][NW] position codes (L, R, C), shared by the block
+};
+
+// Fisher-Yates from 16-bit Philox chunks: for i = n-1 .. 1: j = (chunk * (i+1)) >> 16; swap(i, j)
+template <int NS>
+SRNN_DEV void philox_perm(uint64_t seed, uint64_t slot, uint64_t epoch, uint8_t *ord, int stride) {
+#pragma unroll
+    for (int i = 0; i < NS; ++i) ord[i * stride] = (uint8_t)i;
+    U4 x{0, 0, 0, 0};
+    int have = 0;
+    uint32_t blk = 0;
+    for (int i = NS - 1; i >= 1; --i) {
+        if ((have & 7) == 0) x = rng4(seed, ST_PERM, slot, (uint32_t)epoch, ((uint32_t)(epoch >> 32) << 8) | blk++);
+        const uint32_t word = word_of(x, (have & 7) >> 1);
+        const uint32_t chunk = (have & 1) ? (word >> 16) : (word & 0xFFFFu);
+        ++have;
+        const int j = (int)((chunk * (uint32_t)(i + 1)) >> 16);
+        const uint8_t tmp = ord[i * stride];
+        ord[i * stride] = ord[j * stride];
+        ord[j * stride] = tmp;
+    }
+}
+
+// One Keras epoch of the student `w` on the samples frozen in sc.tgt; returns the f64 mean sample loss.
+template <class S>
+SRNN_DEV double train_epoch(float *w, const SgdScratch &sc, bool ordered, float lr) {
+    if constexpr (S::KIND == SRNN_KIND_WW) {  // compute_samples, code/network.py:281-289
+        double acc = 0.0;
+        for (int q = 0; q < S::NW; ++q) {
+            const int k = ordered ? (int)sc.ord[q * sc.stride] : q;
+            const float v = sc.tgt[k * sc.stride];
+            const float x[4] = {v, sc.codes[k], sc.codes[S::NW + k], sc.codes[2 * S::NW + k]};
+            acc = __dadd_rn(acc, (double)mlp_sgd_sample<S>(w, x, &v, lr));
+        }
+        return __ddiv_rn(acc, (double)S::NW);
+    } else if constexpr (S::KIND == SRNN_KIND_AGG) {  // compute_samples, code/network.py:414-417
+        float t[S::NW], agg[S::AGGS];
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) t[k] = sc.tgt[k * sc.stride];
+        agg_means<S>(t, agg);
+        return (double)mlp_sgd_sample<S>(w, agg, agg, lr);
+    } else {
+        float t[S::NW];
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) t[k] = sc.tgt[k * sc.stride];
+        return (double)rnn_sgd_sample<S>(w, t, lr);
+    }
+}
+
+template <class S>
+SRNN_DEV void fill_codes(float *codes) {  // by one thread
+    if constexpr (S::KIND == SRNN_KIND_WW) {
+        static_for<0, S::NW>([&](auto K) {
+            constexpr int k = decltype(K)::value;
+            codes[k] = S::codeL(k);
+            codes[S::NW + k] = S::codeR(k);
+            codes[2 * S::NW + k] = S::codeC(k);
+        });
+    }
+}
+
+}  // namespace srnn

@@ -1,0 +1,359 @@
+"""GPU parity tests: the CUDA path (through the C ABI of libsrnn_b200.so) against the CPU oracle.
+
+Bar: FP32 weights bit-for-bit (NaN matches NaN), integer outputs (steps, classes, counters, actions) exactly.
+Sizes are what the oracle finishes in seconds; the full-size checks use size-independent properties.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from util_parity import assert_same_weights, glorot_population
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(0, 2, 2, 0), (0, 3, 2, 0), (0, 2, 3, 0), (0, 2, 1, 0), (1, 2, 2, 4), (1, 2, 2, 3), (1, 3, 2, 4),
+          (2, 2, 2, 0), (2, 2, 1, 0)]
+BENCH_SHAPES = [(0, 2, 2, 0), (1, 2, 2, 4), (2, 2, 2, 0)]
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import srnn_engine
+    srnn_engine.lib()
+    return srnn_engine
+
+
+def both(eng, key):
+    kind, width, depth, aggs = key
+    return eng.make_desc(kind, width, depth, aggs), oracle.desc(kind, width, depth, aggs)
+
+
+def test_descs_agree(eng):
+    for key in SHAPES:
+        dg, do = both(eng, key)
+        assert dg.n_weights == do.n_weights
+        assert eng.shape_supported(dg)
+    assert not eng.shape_supported(eng.make_desc(0, 5, 5))
+
+
+# ---------------------------------------------------------------- K1 self-application
+@pytest.mark.parametrize("key", SHAPES)
+def test_self_apply_fixed_bitwise(eng, key):
+    """n_steps unconditional self-applications: weights bit-for-bit, including ragged tile sizes."""
+    dg, do = both(eng, key)
+    for n, steps in [(1, 1), (255, 3), (257, 2), (5000, 10), (4096, 101)]:
+        w = glorot_population(key, n, seed=n + steps)
+        pop = eng.Population.from_numpy(dg, w)
+        pop.self_apply(steps)
+        ref = w.copy()
+        oracle.self_apply(do, ref, steps)
+        assert_same_weights(pop.numpy(), ref, "%r n=%d steps=%d" % (key, n, steps))
+
+
+@pytest.mark.parametrize("key", BENCH_SHAPES)
+def test_self_apply_strided_records(eng, key):
+    """ld > n_weights (padded records) takes the un-staged path."""
+    dg, do = both(eng, key)
+    n = 1000
+    w = glorot_population(key, n, seed=4)
+    pad = np.zeros((n, dg.n_weights + 3), np.float32)
+    pad[:, :dg.n_weights] = w
+    pop = eng.Population.from_numpy(dg, pad)
+    pop.self_apply(7)
+    ref = w.copy()
+    oracle.self_apply(do, ref, 7)
+    assert_same_weights(pop.numpy(), ref)
+    assert (pop.w[:, dg.n_weights:].cpu().numpy() == 0).all()
+
+
+@pytest.mark.parametrize("key", SHAPES)
+@pytest.mark.parametrize("eps", [1e-14, 1e-4])
+def test_run_net_until_and_classes(eng, key, eps):
+    """run_net stop rule + fused classification: steps, classes, counters exact; weights and trajectories bitwise."""
+    dg, do = both(eng, key)
+    n = 3000
+    w = glorot_population(key, n, seed=7)
+    w[0] = 0.0
+    pop = eng.Population.from_numpy(dg, w)
+    out = pop.self_apply(100, mode=eng.RUN_UNTIL, eps=eps, want_steps=True, want_cls=True, want_counters=True,
+                         want_traj=(key in BENCH_SHAPES))
+    ref = w.copy()
+    if key in BENCH_SHAPES:
+        steps, traj = oracle.self_apply(do, ref, 100, mode=oracle.RUN_UNTIL, eps=eps, traj=True)
+    else:
+        steps = oracle.self_apply(do, ref, 100, mode=oracle.RUN_UNTIL, eps=eps)
+    cls, cnt = oracle.classify(do, ref, eps)
+    assert np.array_equal(out["steps"].cpu().numpy(), steps)
+    assert_same_weights(pop.numpy(), ref)
+    assert np.array_equal(out["cls"].cpu().numpy(), cls)
+    assert out["counters"].cpu().numpy().tolist() == cnt.tolist()
+    if key in BENCH_SHAPES:
+        gt = out["traj"].cpu().numpy()
+        for i in range(0, n, 37):
+            assert_same_weights(gt[:steps[i], i, :dg.n_weights], traj[:steps[i], i], "traj %d" % i)
+
+
+def test_golden_ww_run_net(eng, golden_dir):
+    """The reference's own 20 WW(2,2) trajectories, free-running on the GPU from the golden initial weights:
+    counters {11 divergent, 9 fix_zero}, saved-state counts and every stored state bit-for-bit."""
+    g = np.load(os.path.join(golden_dir, "ww_self_application.npz"))
+    W, P = g["weights"], g["particle"]
+    uids = np.unique(P)
+    init = np.ascontiguousarray(np.stack([W[P == u][0] for u in uids]))
+    dg, _ = both(eng, (0, 2, 2, 0))
+    pop = eng.Population.from_numpy(dg, init)
+    out = pop.self_apply(100, mode=eng.RUN_UNTIL, eps=1e-14, want_steps=True, want_counters=True, want_traj=True)
+    assert out["counters"].cpu().numpy().tolist() == [11, 9, 0, 0, 0]
+    steps, traj = out["steps"].cpu().numpy(), out["traj"].cpu().numpy()
+    for i, u in enumerate(uids):
+        S = W[P == u]
+        saved = 1 + sum(np.isfinite(traj[s, i]).all() for s in range(steps[i]))
+        assert saved == len(S)
+        for s in range(1, len(S)):
+            assert_same_weights(traj[s - 1, i], S[s], "golden particle %d step %d" % (u, s))
+
+
+def test_golden_agg_teacher_forced(eng, golden_dir):
+    g = np.load(os.path.join(golden_dir, "agg_self_application.npz"))
+    W, P, T = g["weights"], g["particle"], g["time"]
+    pairs = [(i, i + 1) for i in range(len(P) - 1) if P[i] == P[i + 1] and T[i + 1] == T[i] + 1]
+    dg, _ = both(eng, (1, 2, 2, 4))
+    pop = eng.Population.from_numpy(dg, W[[p[0] for p in pairs]])
+    pop.self_apply(1)
+    assert_same_weights(pop.numpy(), W[[p[1] for p in pairs]])
+
+
+# ---------------------------------------------------------------- K2/K3/K4 attack pairs
+@pytest.mark.parametrize("key", SHAPES)
+def test_apply_pairs(eng, key):
+    dg, do = both(eng, key)
+    n = 2048
+    w = glorot_population(key, n, seed=9)
+    rng = np.random.default_rng(1)
+    victims = rng.permutation(n)[: n // 2]
+    rest = np.setdiff1d(np.arange(n), victims)
+    attackers = rng.choice(rest, size=victims.size)
+    pop = eng.Population.from_numpy(dg, w)
+    pop.attack(attackers, victims)
+    ref = w.copy()
+    oracle.apply(do, ref, attackers, ref, victims, ref, victims, victims.size)
+    assert_same_weights(pop.numpy(), ref)
+    # self-attack through the pair path (op = in = out)
+    pop.attack(rest[:100], rest[:100])
+    oracle.apply(do, ref, rest[:100], ref, rest[:100], ref, rest[:100], 100)
+    assert_same_weights(pop.numpy(), ref)
+
+
+# ---------------------------------------------------------------- K6 classify / predicates
+@pytest.mark.parametrize("key", SHAPES)
+def test_classify_and_flags(eng, key):
+    dg, do = both(eng, key)
+    n = 4000
+    w = glorot_population(key, n, seed=12)
+    oracle.self_apply(do, w, 3)            # a mix of shrinking, growing and non-finite nets
+    w[1] = 0.0
+    w[2, 0] = np.inf
+    w[3, -1] = np.nan
+    if key == (0, 2, 2, 0):
+        w[4] = 0.0
+        w[4, [0, 8, 12]] = 1.0              # the identity fixpoint: fix_other
+    for eps in (1e-14, 1e-4, 0.5):
+        pop = eng.Population.from_numpy(dg, w)
+        for fs in (True, False):
+            cls, cnt, flags = pop.classify(eps, with_fix_sec=fs, want_flags=True)
+            rcls, rcnt = oracle.classify(do, w, eps, with_fix_sec=fs)
+            assert np.array_equal(cls.cpu().numpy(), rcls)
+            assert cnt.cpu().numpy().tolist() == rcnt.tolist()
+        assert np.array_equal(flags.cpu().numpy(), oracle.predicates(do, w, eps))
+
+
+# ---------------------------------------------------------------- K7 init
+@pytest.mark.parametrize("key", SHAPES)
+def test_init_bitwise(eng, key):
+    dg, do = both(eng, key)
+    n = 3000
+    pop = eng.Population(dg, n)
+    pop.init(seed=1234, slot0=77, generation=5)
+    ref = np.zeros((n, do.n_weights), np.float32)
+    oracle.init(do, ref, seed=1234, slot0=77, generation=5)
+    assert_same_weights(pop.numpy(), ref)
+    idx = np.array([5, 17, 2999])
+    pop.init(seed=99, slot0=0, generation=1, idx=idx)
+    oracle.init(do, ref, seed=99, slot0=0, generation=1, idx=idx)
+    assert_same_weights(pop.numpy(), ref)
+
+
+# ---------------------------------------------------------------- K5 train / learn_from
+@pytest.mark.parametrize("key", SHAPES)
+@pytest.mark.parametrize("perm_mode", [0, 1, 2])
+def test_train_bitwise(eng, key, perm_mode):
+    dg, do = both(eng, key)
+    n, epochs = 700, 12
+    w = glorot_population(key, n, seed=21)
+    ns = dg.n_weights if key[0] == 0 else 1
+    perm = None
+    if perm_mode == 1:
+        rs = np.random.RandomState(5)
+        perm = np.stack([rs.permutation(ns) for _ in range(epochs)]).astype(np.uint8)
+    pop = eng.Population.from_numpy(dg, w)
+    loss = pop.train(epochs, lr=0.01, perm_mode=perm_mode, perm=perm, seed=3, slot0=10, epoch0=4)
+    ref = w.copy()
+    rloss = oracle.train(do, ref, epochs, lr=0.01, perm_mode=perm_mode, perm=perm, seed=3, slot0=10, epoch0=4)
+    assert_same_weights(pop.numpy(), ref, "train %r perm=%d" % (key, perm_mode))
+    gl = loss.cpu().numpy()
+    assert np.array_equal(np.isnan(gl), np.isnan(rloss))
+    m = ~np.isnan(gl)
+    assert np.array_equal(gl[m], rloss[m])
+
+
+@pytest.mark.parametrize("key", SHAPES)
+def test_learn_from_bitwise(eng, key):
+    dg, do = both(eng, key)
+    n = 600
+    w = glorot_population(key, n, seed=31)
+    t = glorot_population(key, n, seed=32)
+    tidx = np.random.default_rng(2).integers(0, n, n)
+    pop, tea = eng.Population.from_numpy(dg, w), eng.Population.from_numpy(dg, t)
+    pop.train(5, perm_mode=2, seed=8, teacher=tea, teacher_idx=tidx)
+    ref = w.copy()
+    oracle.train(do, ref, 5, perm_mode=2, seed=8, teacher_w=t, teacher_idx=tidx)
+    assert_same_weights(pop.numpy(), ref)
+
+
+def test_training_reaches_fixpoints(eng):
+    """training-fixpoints.py statistic at population scale: 1000 epochs -> WW all fix_other, AGG all other (eps 1e-4)."""
+    dg, _ = both(eng, (0, 2, 2, 0))
+    pop = eng.Population(dg, 10000).init(seed=5)
+    pop.train(1000, perm_mode=2, seed=6, want_loss=False)
+    cnt = pop.classify(1e-4)[1].cpu().numpy()
+    assert cnt[2] >= 9700, cnt
+    dg, _ = both(eng, (1, 2, 2, 4))
+    pop = eng.Population(dg, 10000).init(seed=5)
+    pop.train(1000, want_loss=False)
+    cnt = pop.classify(1e-4)[1].cpu().numpy()
+    assert cnt[4] >= 9000, cnt
+
+
+# ---------------------------------------------------------------- K9 known-fixpoint variation
+def test_kfv_bitwise_and_statistics(eng, golden_dir):
+    dg, do = both(eng, (0, 2, 2, 0))
+    base = np.zeros(14, np.float32)
+    base[[0, 8, 12]] = 1.0
+    g = np.load(os.path.join(golden_dir, "kfv.npz"))
+    scale = 1.0
+    for level in range(10):
+        n = 20000
+        out = eng.kfv(dg, base, n, scale, level, 100, 1e-4, seed=99, slot0=5, want_weights=True)
+        ys, zs, wr = oracle.kfv(do, base, n, scale, level, 100, 1e-4, seed=99, slot0=5, want_weights=True)
+        assert np.array_equal(out["ys"].cpu().numpy(), ys)
+        assert np.array_equal(out["zs"].cpu().numpy(), zs)
+        assert_same_weights(out["w"].cpu().numpy(), wr)
+        hist = out["hist"].cpu().numpy()
+        assert np.array_equal(hist[0], np.bincount(ys, minlength=101))
+        assert np.array_equal(hist[1], np.bincount(zs, minlength=101))
+        ry = g["ys"][level * 100:(level + 1) * 100]
+        assert abs(ys.mean() - ry.mean()) < 4 * max(ry.std(), 0.3) / 10 + 0.1
+        scale /= 10.0
+
+
+# ---------------------------------------------------------------- K8 soup
+@pytest.mark.parametrize("key", BENCH_SHAPES)
+def test_soup_ordered_bitwise(eng, key):
+    """Exact-order Soup.evolve: a few generations with attacks, learn_from, training and culling."""
+    dg, do = both(eng, key)
+    n = 40
+    w = glorot_population(key, n, seed=41)
+    w[3] = 0.0
+    rng = np.random.default_rng(6)
+    pg = eng.make_soup_params(attacking_rate=0.3, learn_from_rate=0.3, train=2, learn_from_severity=2,
+                              remove_divergent=True, remove_zero=True, epsilon=1e-4, perm_mode=2)
+    po = oracle.soup_params(attacking_rate=0.3, learn_from_rate=0.3, train=2, learn_from_severity=2,
+                            remove_divergent=True, remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pop = eng.Population.from_numpy(dg, w)
+    ref = w.copy()
+    for gen in range(1, 6):
+        att = np.where(rng.random(n) < 0.3, rng.integers(0, n, n), -1)
+        lrn = np.where(rng.random(n) < 0.3, rng.integers(0, n, n), -1)
+        action, loss, logged = pop.soup_ordered(pg, att, lrn, seed=17, gen=gen, want_logged=True)
+        ra, rl, rlog = oracle.soup_ordered(do, po, ref, att, lrn, seed=17, gen=gen, want_logged=True)
+        assert_same_weights(pop.numpy(), ref, "gen %d" % gen)
+        assert np.array_equal(action.cpu().numpy(), ra)
+        assert_same_weights(logged.cpu().numpy(), rlog)
+        gl = loss.cpu().numpy()
+        assert np.array_equal(np.isnan(gl), np.isnan(rl)) and np.array_equal(gl[~np.isnan(gl)], rl[~np.isnan(rl)])
+
+
+@pytest.mark.parametrize("key", BENCH_SHAPES)
+@pytest.mark.parametrize("train,sev", [(0, 1), (2, 3)])
+def test_soup_sync_bitwise_and_shard_invariance(eng, key, train, sev):
+    """Snapshot-synchronous generations: one owner of all particles == the oracle, and two owners of half the
+    population each (the multi-GPU sharding, emulated on one device) produce the same arena."""
+    import torch
+    dg, do = both(eng, key)
+    n = 3000
+    kw = dict(attacking_rate=0.4, learn_from_rate=0.2, train=train, learn_from_severity=sev, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population(key, n, seed=51)
+    snap = torch.from_numpy(w).cuda()
+    ref = w.copy()
+    scratch = torch.zeros(2 * n, dtype=torch.int32, device="cuda")
+    for gen in range(1, 4):
+        out = torch.zeros_like(snap)
+        action = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        dead = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        eng.soup_sync(dg, pg, snap, n, out, 0, n, 23, gen, scratch, action=action, dead=dead)
+        rout = np.zeros_like(ref)
+        ra, rl, natt = oracle.soup_sync(do, po, ref, n, rout, 0, n, 23, gen)
+        assert natt > 0.3 * n
+        assert_same_weights(out.cpu().numpy(), rout, "gen %d" % gen)
+        assert np.array_equal(action.cpu().numpy(), ra)
+        # sharded: two owners
+        half = n // 2 + 7
+        o2 = torch.zeros_like(snap)
+        eng.soup_sync(dg, pg, snap, n, o2[:half], 0, half, 23, gen, scratch)
+        eng.soup_sync(dg, pg, snap, n, o2[half:], half, n - half, 23, gen, scratch)
+        assert torch.equal(o2.view(torch.int32), out.view(torch.int32))
+        # uid allocation for the respawned particles
+        uid = torch.arange(n, dtype=torch.int64, device="cuda")
+        tmp = torch.zeros((n + 1023) // 1024 + 1, dtype=torch.int64, device="cuda")
+        nd = torch.zeros(1, dtype=torch.int64, device="cuda")
+        eng.assign_uids(dead, uid, 10 ** 6, tmp, nd)
+        dn = dead.cpu().numpy().astype(bool)
+        want = np.arange(n)
+        want[dn] = 10 ** 6 + np.arange(dn.sum())
+        assert np.array_equal(uid.cpu().numpy(), want) and int(nd.item()) == int(dn.sum())
+        snap, ref = out, rout
+
+
+# ---------------------------------------------------------------- full-size, size-independent properties
+def test_full_size_properties(eng):
+    """2^22 WW(2,2) nets x 100 steps (the bench workload's shape): (i) the identity fixpoint is invariant,
+    (ii) two runs are bit-identical, (iii) a strided 1/1024 sample equals the oracle, (iv) class counts of the
+    whole population equal the sum over shards."""
+    import torch
+    dg, do = both(eng, (0, 2, 2, 0))
+    n = 1 << 22
+    pop = eng.Population(dg, n).init(seed=0)
+    pop.w[::4096] = 0.0
+    pop.w[::4096, 0] = 1.0
+    pop.w[::4096, 8] = 1.0
+    pop.w[::4096, 12] = 1.0
+    start = pop.w.clone()
+    pop.self_apply(100)
+    first = pop.w.clone()
+    assert torch.equal(first[::4096].view(torch.int32), start[::4096].view(torch.int32))
+    pop.w.copy_(start)
+    pop.self_apply(100)
+    assert torch.equal(pop.w.view(torch.int32), first.view(torch.int32))
+    sample = np.ascontiguousarray(start[5::1024].cpu().numpy())
+    oracle.self_apply(do, sample, 100)
+    assert_same_weights(first[5::1024].cpu().numpy(), sample)
+    cls, cnt = pop.classify(1e-4)
+    parts = sum(eng.Population(dg, n // 4, w=first[q * (n // 4):(q + 1) * (n // 4)]).classify(1e-4)[1] for q in range(4))
+    assert torch.equal(cnt, parts) and int(cnt.sum()) == n
+    rc, rcnt = oracle.classify(do, sample, 1e-4)
+    assert np.array_equal(cls[5::1024].cpu().numpy(), rc)
