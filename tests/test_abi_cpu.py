@@ -49,7 +49,7 @@ def test_bad_shapes_are_errors_not_crashes():
         eng.make_desc(0, 99, 2)
     with pytest.raises(eng.SrnnError):
         eng.make_desc(1, 1, 3, 4)          # 10 weights, 4 aggregates: leftovers (2) fill another collection
-    assert not eng.shape_supported(eng.make_desc(0, 4, 4))
+    assert not eng.shape_supported(eng.make_desc(0, 4, 3))
 
 
 def test_no_cpu_fallback():
