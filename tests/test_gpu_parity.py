@@ -36,7 +36,7 @@ def test_descs_agree(eng):
         dg, do = both(eng, key)
         assert dg.n_weights == do.n_weights
         assert eng.shape_supported(dg)
-    assert not eng.shape_supported(eng.make_desc(0, 5, 5))
+    assert not eng.shape_supported(eng.make_desc(0, 4, 3))
 
 
 # ---------------------------------------------------------------- K1 self-application
