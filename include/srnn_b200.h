@@ -46,6 +46,14 @@ int srnn_apply(const srnn_net_desc *d, const float *op_w, int64_t op_ld, const i
                const float *in_w, int64_t in_ld, const int32_t *in_idx,
                float *out_w, int64_t out_ld, const int32_t *out_idx, int64_t n, void *stream);
 
+/* NeuralNetwork.apply(*inputs) = model.predict on one input row (WeightwiseNeuralNetwork.apply
+ * code/network.py:235-237, AggregatingNeuralNetwork.apply :355-357, RecurrentNeuralNetwork.apply :540-542):
+ * WW / AGG: x = float[n][io] -> y = float[n][out] (io = 4 / aggregates, out = 1 / aggregates);
+ * RNN: x = float[n][n_weights] (a sequence as long as the weight list) -> y = float[n][n_weights].
+ * Row p is evaluated by the net in record idx[p] (NULL = p).  x, y: device pointers. */
+int srnn_forward(const srnn_net_desc *d, const float *w, int64_t ld, const int32_t *idx, const float *x, float *y,
+                 int64_t n, void *stream);
+
 /* NeuralNetwork.self_attack(n_steps) (code/network.py:124-127) for every net, weights register-resident
  * for the whole run; mode SRNN_RUN_UNTIL adds FixpointExperiment.run_net's stop rule
  * (code/experiment.py:70-77: stop when is_diverged() or is_fixpoint()).
@@ -96,10 +104,15 @@ int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double s
  * every write visible to later particles.  att / lrn = int64[n] target index or -1 per particle (drawn
  * by the host in the reference's order, soup.py:56-63).  Outputs (nullable): action uint8[n]
  * (SRNN_ACT_*), loss double[n] (last train epoch, NaN if none), logged float[n][ld] = the weights
- * particle.save_state (soup.py:87) logs for the old particle.  Meant for the setups' soups (10-100 nets). */
+ * particle.save_state (soup.py:87) logs for the old particle.  Respawn (generate_particle, soup.py:78,83):
+ * if `spares` (float[n_spares][spare_ld], nullable) still holds unused records -- fresh nets the host's
+ * generator() produced ahead of time -- the next one is consumed, in particle order; otherwise the record is
+ * re-initialised like srnn_init(seed, slot, gen).  *spares_used (device int32, nullable) = records consumed.
+ * Meant for the setups' soups (10-100 nets). */
 int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n,
                       const int64_t *att, const int64_t *lrn, uint64_t seed, uint64_t gen, uint8_t *action,
-                      double *loss, float *logged, void *stream);
+                      double *loss, float *logged, const float *spares, int64_t spare_ld, int32_t n_spares,
+                      int32_t *spares_used, void *stream);
 
 /* Soup.evolve, snapshot-synchronous generation for large / sharded soups (DESIGN.md "Soup modes"): every
  * partner is read from `snap`, the start-of-generation arena of ALL n_total particles (after the

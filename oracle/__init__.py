@@ -192,20 +192,40 @@ def soup_draw(p, seed, gen, n_total, slot0=0, n=None):
     return att, lrn
 
 
-def soup_ordered(d, p, w, att, lrn, seed, gen, n=None, want_logged=False):
+def forward(d, w, x, idx=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n = x.shape[0]
+    io_out = x.shape[1] if d.kind == KIND_RNN else (1 if d.kind == KIND_WW else d.aggregates)
+    y = np.zeros((n, io_out), np.float32)
+    keep = _i32(idx)
+    pw, ld = _f32(w)
+    _chk(lib().srnn_oracle_forward(C.byref(d), pw, ld, keep[1] if keep else None, x.ctypes.data_as(C.POINTER(C.c_float)),
+                                   y.ctypes.data_as(C.POINTER(C.c_float)), C.c_int64(n)))
+    return y
+
+
+def soup_ordered(d, p, w, att, lrn, seed, gen, n=None, want_logged=False, spares=None):
     n = w.shape[0] if n is None else n
     att = np.ascontiguousarray(att, dtype=np.int64)
     lrn = np.ascontiguousarray(lrn, dtype=np.int64)
     action = np.zeros(n, np.uint8)
     loss = np.full(n, np.nan, np.float64)
     logged = np.zeros_like(w) if want_logged else None
+    used = C.c_int32(0)
+    if spares is not None:
+        spares = np.ascontiguousarray(spares, dtype=np.float32)
     pw, ld = _f32(w)
     _chk(lib().srnn_oracle_soup_ordered(C.byref(d), C.byref(p), pw, ld, C.c_int64(n),
                                         att.ctypes.data_as(C.POINTER(C.c_int64)),
                                         lrn.ctypes.data_as(C.POINTER(C.c_int64)), C.c_uint64(seed), C.c_uint64(gen),
                                         action.ctypes.data_as(C.POINTER(C.c_uint8)),
                                         loss.ctypes.data_as(C.POINTER(C.c_double)),
-                                        logged.ctypes.data_as(C.POINTER(C.c_float)) if want_logged else None))
+                                        logged.ctypes.data_as(C.POINTER(C.c_float)) if want_logged else None,
+                                        spares.ctypes.data_as(C.POINTER(C.c_float)) if spares is not None else None,
+                                        C.c_int64(spares.shape[1] if spares is not None else 0),
+                                        C.c_int32(spares.shape[0] if spares is not None else 0), C.byref(used)))
+    if spares is not None:
+        return (action, loss, logged, used.value) if want_logged else (action, loss, used.value)
     return (action, loss, logged) if want_logged else (action, loss)
 
 

@@ -280,6 +280,25 @@ int srnn_oracle_apply(const srnn_net_desc *d, const float *op_w, int64_t op_ld, 
     return SRNN_OK;
 }
 
+/* ================================================================== exported: raw forward */
+/* NeuralNetwork.apply(*inputs): model.predict on one input row (code/network.py:235-237, :355-357, :540-542).
+ * WW/AGG: x[n][io] -> y[n][out];  RNN: x[n][T] -> y[n][T] with T = n_weights. */
+int srnn_oracle_forward(const srnn_net_desc *d, const float *w, int64_t ld, const int32_t *idx, const float *x,
+                        float *y, int64_t n) {
+    shape_t s;
+    int rc = make_shape(d, &s);
+    if (rc) return rc;
+    unsigned csr = ftz_on();
+    for (int64_t p = 0; p < n; ++p) {
+        float op[MAXW];
+        load_net(w, ld, idx ? idx[p] : p, s.n_weights, op);
+        if (s.kind == SRNN_KIND_RNN) rnn_forward_seq(&s, op, x + p * s.n_weights, s.n_weights, y + p * s.n_weights, NULL);
+        else mlp_forward(&s, op, x + p * s.in[0], y + p * s.out[s.n_layers - 1]);
+    }
+    ftz_restore(csr);
+    return SRNN_OK;
+}
+
 /* ================================================================== exported: self-application */
 /* mode SRNN_RUN_FIXED: n_steps x self_attack (code/network.py:124-127), steps_out = n_steps.
  * mode SRNN_RUN_UNTIL: FixpointExperiment.run_net (code/experiment.py:70-77):
@@ -664,7 +683,8 @@ int srnn_oracle_soup_draw(const srnn_soup_params *p, uint64_t seed, uint64_t gen
  * cull tests on the OLD particle, respawn keyed by (slot, generation). */
 static void soup_particle_tail(const shape_t *s, const srnn_soup_params *p, float *cur, const float *teacher,
                                int teacher_is_self, uint64_t seed, uint64_t slot, uint64_t gen, uint8_t *action, double *loss,
-                               float *logged /* weights of the old particle after its events */) {
+                               float *logged /* weights of the old particle after its events */,
+                               const float *spares, int64_t spare_ld, int32_t n_spares, int32_t *spares_used) {
     uint8_t order[MAXW];
     int ns = n_samples_of(s);
     int sev = p->learn_from_severity > 0 ? p->learn_from_severity : 0;
@@ -692,7 +712,15 @@ static void soup_particle_tail(const shape_t *s, const srnn_soup_params *p, floa
     int dead = 0;
     if (p->remove_divergent && is_diverged(cur, s->n_weights)) { dead = 1; *action = SRNN_ACT_DIV_DEAD; }
     if (p->remove_zero && is_zero(cur, s->n_weights, p->epsilon)) { dead = 1; *action = SRNN_ACT_ZERO_DEAD; }
-    if (dead) init_net(s, seed, slot, (uint32_t)gen, cur);
+    if (dead) {
+        /* respawn: the next caller-supplied spare record (generator() output) if any is left, else Philox init */
+        if (spares && spares_used && *spares_used < n_spares) {
+            load_net(spares, spare_ld, *spares_used, s->n_weights, cur);
+            ++*spares_used;
+        } else {
+            init_net(s, seed, slot, (uint32_t)gen, cur);
+        }
+    }
 }
 
 /* Exact-order generation = Soup.evolve (code/soup.py:51-87): particles visited in index order, every
@@ -701,11 +729,13 @@ static void soup_particle_tail(const shape_t *s, const srnn_soup_params *p, floa
  * train epoch (NaN if none), logged[i*ld+k] = weights save_state would log for the old particle. */
 int srnn_oracle_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n,
                              const int64_t *att, const int64_t *lrn, uint64_t seed, uint64_t gen, uint8_t *action,
-                             double *loss, float *logged) {
+                             double *loss, float *logged, const float *spares, int64_t spare_ld, int32_t n_spares,
+                             int32_t *spares_used) {
     shape_t s;
     int rc = make_shape(d, &s);
     if (rc) return rc;
     unsigned csr = ftz_on();
+    if (spares_used) *spares_used = 0;
     for (int64_t i = 0; i < n; ++i) {
         float cur[MAXW], oth[MAXW], res[MAXW], lg[MAXW];
         uint8_t act = SRNN_ACT_NONE;
@@ -721,7 +751,8 @@ int srnn_oracle_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, 
         int has_teacher = lrn && lrn[i] >= 0 && lrn[i] != i;
         int self_teacher = lrn && lrn[i] == i; /* samples recomputed per call: code/network.py:623 */
         if (has_teacher) load_net(w, ld, lrn[i], s.n_weights, oth);
-        soup_particle_tail(&s, p, cur, has_teacher ? oth : NULL, self_teacher, seed, (uint64_t)i, gen, &act, &ls, lg);
+        soup_particle_tail(&s, p, cur, has_teacher ? oth : NULL, self_teacher, seed, (uint64_t)i, gen, &act, &ls, lg,
+                           spares, spare_ld, n_spares, spares_used);
         store_net(w, ld, i, s.n_weights, cur);
         if (action) action[i] = act;
         if (loss) loss[i] = ls;
@@ -776,7 +807,8 @@ int srnn_oracle_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, con
                 memcpy(cur, res, sizeof(float) * s.n_weights);
             }
             if (lr_ >= 0) load_net(snap, snap_ld, lr_, s.n_weights, oth);
-            soup_particle_tail(&s, p, cur, lr_ >= 0 ? oth : NULL, 0, seed, (uint64_t)(slot0 + i), gen, &act, &ls, NULL);
+            soup_particle_tail(&s, p, cur, lr_ >= 0 ? oth : NULL, 0, seed, (uint64_t)(slot0 + i), gen, &act, &ls, NULL,
+                               NULL, 0, 0, NULL);
             store_net(w_out, out_ld, i, s.n_weights, cur);
             if (action) action[i] = act;
             if (loss) loss[i] = ls;

@@ -194,6 +194,33 @@ __global__ void __launch_bounds__(BS) apply_kernel(const float *op_w, int64_t op
     record_store<S::NW>(out_w, out_ld, out_idx ? out_idx[p] : p, out);
 }
 
+// ================================================================================================ raw forward
+// NeuralNetwork.apply(*inputs) = model.predict on one row (code/network.py:235-237, :355-357, :540-542)
+template <class S>
+__global__ void __launch_bounds__(BS) forward_kernel(const float *__restrict__ w, int64_t ld,
+                                                     const int32_t *__restrict__ idx, const float *__restrict__ x,
+                                                     float *__restrict__ y, int64_t n) {
+    const int64_t p = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (p >= n) return;
+    float op[S::NW];
+    record_load<S::NW>(w, ld, idx ? idx[p] : p, op);
+    if constexpr (S::KIND == SRNN_KIND_RNN) {
+        float seq[S::NW], out[S::NW];
+#pragma unroll
+        for (int t = 0; t < S::NW; ++t) seq[t] = x[p * S::NW + t];
+        rnn_forward_seq<S, false>(op, seq, out, nullptr);
+#pragma unroll
+        for (int t = 0; t < S::NW; ++t) y[p * S::NW + t] = out[t];
+    } else {
+        float in[S::IO], out[S::OUTW];
+#pragma unroll
+        for (int q = 0; q < S::IO; ++q) in[q] = x[p * S::IO + q];
+        mlp_forward<S>(op, in, out);
+#pragma unroll
+        for (int q = 0; q < S::OUTW; ++q) y[p * S::OUTW + q] = out[q];
+    }
+}
+
 // ================================================================================================ K6 classify
 template <class S>
 __global__ void __launch_bounds__(BS) classify_kernel(const float *__restrict__ w, int64_t ld, int64_t n, Eps eps,
@@ -360,7 +387,8 @@ template <class S>
 __device__ __forceinline__ void soup_tail(const SoupP &p, float *cur, const SgdScratch &sc, bool has_teacher,
                                           bool teacher_is_self, uint64_t seed, uint64_t slot, uint64_t gen,
                                           const Limits &lim, uint8_t *action, double *loss, float *logged,
-                                          int64_t logged_ld, int64_t logged_i, bool *dead) {
+                                          int64_t logged_ld, int64_t logged_i, bool *dead, const float *spares = nullptr,
+                                          int64_t spare_ld = 0, int n_spares = 0, int *spares_used = nullptr) {
     const int sev = p.severity > 0 ? p.severity : 0, tr = p.train > 0 ? p.train : 0;
     const uint64_t ep = gen * (uint64_t)(sev + tr);
     const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
@@ -386,7 +414,16 @@ __device__ __forceinline__ void soup_tail(const SoupP &p, float *cur, const SgdS
     bool d = false;
     if (p.remove_divergent && is_diverged<S::NW>(cur)) { d = true; *action = SRNN_ACT_DIV_DEAD; }
     if (p.remove_zero && is_zero<S::NW>(cur, p.eps.le)) { d = true; *action = SRNN_ACT_ZERO_DEAD; }
-    if (d) init_net<S>(seed, slot, (uint32_t)gen, lim, cur);
+    if (d) {  // respawn: next caller-supplied spare record (generator() output) if one is left, else Philox init
+        if (spares && spares_used && *spares_used < n_spares) {
+            const float *sp = spares + (int64_t)(*spares_used) * spare_ld;
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) cur[k] = sp[k];
+            ++*spares_used;
+        } else {
+            init_net<S>(seed, slot, (uint32_t)gen, lim, cur);
+        }
+    }
     *dead = d;
 }
 
@@ -394,10 +431,13 @@ __device__ __forceinline__ void soup_tail(const SoupP &p, float *cur, const SgdS
 template <class S>
 __global__ void soup_ordered_kernel(float *w, int64_t ld, int64_t n, const int64_t *__restrict__ att,
                                     const int64_t *__restrict__ lrn, SoupP p, uint64_t seed, uint64_t gen,
-                                    Limits lim, uint8_t *action, double *loss, float *logged) {
+                                    Limits lim, uint8_t *action, double *loss, float *logged,
+                                    const float *__restrict__ spares, int64_t spare_ld, int n_spares,
+                                    int *spares_used_out) {
     extern __shared__ __align__(16) unsigned char smem[];
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     SgdScratch sc = sgd_scratch<S>(smem, 1);
+    int used = 0;
     for (int64_t i = 0; i < n; ++i) {
         float cur[S::NW], oth[S::NW], res[S::NW];
         uint8_t act = SRNN_ACT_NONE;
@@ -425,11 +465,13 @@ __global__ void soup_ordered_kernel(float *w, int64_t ld, int64_t n, const int64
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tr[k];
         }
-        soup_tail<S>(p, cur, sc, has_teacher, self_teacher, seed, (uint64_t)i, gen, lim, &act, &ls, logged, ld, i, &dead);
+        soup_tail<S>(p, cur, sc, has_teacher, self_teacher, seed, (uint64_t)i, gen, lim, &act, &ls, logged, ld, i, &dead,
+                     spares, spare_ld, n_spares, &used);
         record_store<S::NW>(w, ld, i, cur);
         if (action) action[i] = act;
         if (loss) loss[i] = ls;
     }
+    if (spares_used_out) *spares_used_out = used;
 }
 
 // snapshot-synchronous, phase A: every owner evaluates the same pairing function for ALL global particles and
@@ -681,6 +723,18 @@ int srnn_apply(const srnn_net_desc *d, const float *op_w, int64_t op_ld, const i
     return check_launch("srnn_apply");
 }
 
+int srnn_forward(const srnn_net_desc *d, const float *w, int64_t ld, const int32_t *idx, const float *x, float *y,
+                 int64_t n, void *stream) {
+    if (!d || !x || !y) return fail(SRNN_ERR_ARG, "desc, x or y is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+#define BODY(S)                \
+    SRNN_CHECK_ARENA(w, ld, S) \
+    forward_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, idx, x, y, n);
+    SRNN_DISPATCH(d)
+#undef BODY
+    return check_launch("srnn_forward");
+}
+
 int srnn_self_apply(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t n_steps, int32_t mode, double eps,
                     int32_t with_fix_sec, int32_t *steps_out, uint8_t *cls_out, int64_t *counters, float *traj,
                     void *stream) {
@@ -775,7 +829,8 @@ int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double s
 
 int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n,
                       const int64_t *att, const int64_t *lrn, uint64_t seed, uint64_t gen, uint8_t *action,
-                      double *loss, float *logged, void *stream) {
+                      double *loss, float *logged, const float *spares, int64_t spare_ld, int32_t n_spares,
+                      int32_t *spares_used, void *stream) {
     if (!d) return fail(SRNN_ERR_ARG, "desc is NULL%s");
     if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
     SoupP q;
@@ -784,8 +839,9 @@ int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *
     const Limits lim = make_limits(d);
 #define BODY(S)                                                                                              \
     SRNN_CHECK_ARENA(w, ld, S)                                                                               \
-    soup_ordered_kernel<S><<<1, 32, sgd_smem_bytes<S>(1), (cudaStream_t)stream>>>(w, ld, n, att, lrn, q, seed, gen, lim, \
-                                                                                  action, loss, logged);
+    if (spares && spare_ld < S::NW) return fail(SRNN_ERR_ARG, "spare_ld is smaller than n_weights%s");        \
+    soup_ordered_kernel<S><<<1, 32, sgd_smem_bytes<S>(1), (cudaStream_t)stream>>>(                            \
+        w, ld, n, att, lrn, q, seed, gen, lim, action, loss, logged, spares, spare_ld, spares ? n_spares : 0, spares_used);
     SRNN_DISPATCH(d)
 #undef BODY
     return check_launch("srnn_soup_ordered");

@@ -86,7 +86,7 @@ class FixpointExperiment(Experiment):
         """while i < step_limit and not diverged and not fixpoint: self_attack [; save_state(time=i)]; then count.
         One fused launch when `net` is an engine net (always, unless a user subclass overrides the operator)."""
         fused = getattr(net, "_engine_run_until", None)
-        if fused is not None:
+        if fused is not None and net._fused():
             fused(step_limit, log_states=bool(run_id))
         else:
             i = 0
@@ -99,7 +99,7 @@ class FixpointExperiment(Experiment):
 
     def count(self, net):
         label = getattr(net, "_engine_class_name", None)
-        if label is not None:
+        if label is not None and net._fused():
             label = label()
         elif net.is_diverged():
             label = "divergent"

@@ -27,7 +27,7 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
-           "srnn_apply", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
+           "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
            "srnn_soup_ordered", "srnn_soup_sync", "srnn_assign_uids", "srnn_fp32_probe")
 
 
@@ -240,17 +240,34 @@ class Population:
         self.apply_pairs(attacker_idx, self, victim_idx, self, victim_idx)
 
     # ---- K8
-    def soup_ordered(self, params, att, lrn, seed, gen, want_logged=False):
+    def forward(self, x, idx=None):
+        """NeuralNetwork.apply for a batch of input rows x (n, io) [RNN: (n, n_weights)]; row p uses record idx[p]."""
+        torch = _torch()
+        if not isinstance(x, torch.Tensor):
+            x = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32))
+        x = x.to(device=self.device, dtype=torch.float32).contiguous()
+        n = x.shape[0]
+        cols = self.nw if self.desc.kind == KIND_RNN else (1 if self.desc.kind == KIND_WW else self.desc.aggregates)
+        y = torch.zeros((n, cols), dtype=torch.float32, device=self.device)
+        idx = _idx(idx, self.device)
+        _chk(lib().srnn_forward(*self._args(), _ptr(idx), _ptr(x), _ptr(y), C.c_int64(n), _stream()))
+        return y
+
+    def soup_ordered(self, params, att, lrn, seed, gen, want_logged=False, spares=None):
         torch = _torch()
         att = torch.as_tensor(np.ascontiguousarray(att, dtype=np.int64)).to(self.device)
         lrn = torch.as_tensor(np.ascontiguousarray(lrn, dtype=np.int64)).to(self.device)
         action = torch.zeros(self.n, dtype=torch.uint8, device=self.device)
         loss = torch.full((self.n,), float("nan"), dtype=torch.float64, device=self.device)
         logged = torch.zeros_like(self.w) if want_logged else None
+        used = torch.zeros(1, dtype=torch.int32, device=self.device) if spares is not None else None
         _chk(lib().srnn_soup_ordered(C.byref(self.desc), C.byref(params), _ptr(self.w), C.c_int64(self.ld),
                                      C.c_int64(self.n), _ptr(att), _ptr(lrn), C.c_uint64(seed), C.c_uint64(gen),
-                                     _ptr(action), _ptr(loss), _ptr(logged), _stream()))
-        return (action, loss, logged) if want_logged else (action, loss)
+                                     _ptr(action), _ptr(loss), _ptr(logged), _ptr(spares),
+                                     C.c_int64(spares.shape[1] if spares is not None else 0),
+                                     C.c_int32(spares.shape[0] if spares is not None else 0), _ptr(used), _stream()))
+        out = (action, loss, logged) if want_logged else (action, loss)
+        return out + (used,) if spares is not None else out
 
 
 def soup_sync(desc, params, snap, n_total, w_out, slot0, n, seed, gen, scratch, action=None, loss=None, dead=None):

@@ -1,0 +1,338 @@
+"""GPU tests of the Python face: the reference's class API (network.py / soup.py / experiment.py names and call
+signatures) driving the engine, written the way the reference's code/setups scripts use it, and checked against
+the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from util_parity import assert_same_weights
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def api():
+    import network
+    import soup
+    import experiment
+    network.set_seed(1234)
+    return network, soup, experiment
+
+
+def _flat(net):
+    return net.get_weights_flat()
+
+
+def test_star_import_surface(api):
+    network, soup, experiment = api
+    for name in ("np", "copy", "os", "time", "dill", "tqdm", "K", "WeightwiseNeuralNetwork", "AggregatingNeuralNetwork",
+                 "RecurrentNeuralNetwork", "ParticleDecorator", "TrainingNeuralNetworkDecorator", "NeuralNetwork",
+                 "FixpointExperiment", "Experiment"):
+        assert hasattr(network, name), name
+    assert hasattr(soup, "prng") and hasattr(soup, "Soup")
+    network.K.clear_session()
+    import keras.backend
+    keras.backend.clear_session()
+
+
+@pytest.mark.parametrize("mk,okey", [(lambda n: n.WeightwiseNeuralNetwork(width=2, depth=2), (0, 2, 2, 0)),
+                                     (lambda n: n.AggregatingNeuralNetwork(aggregates=4, width=2, depth=2), (1, 2, 2, 4)),
+                                     (lambda n: n.RecurrentNeuralNetwork(width=2, depth=2), (2, 2, 2, 0))])
+def test_net_methods_match_oracle(api, mk, okey):
+    network, _, _ = api
+    do = oracle.desc(*okey[:3], okey[3])
+    net = mk(network).with_keras_params(activation='sigmoid').with_params(epsilon=1e-4)
+    assert net.get_keras_params()['activation'] == 'sigmoid'          # reported only; the math stays linear
+    w0 = _flat(net)
+    shapes = [m.shape for m in net.get_weights()]
+    assert sum(a * b for a, b in shapes) == do.n_weights and net.get_weights()[0].dtype == np.float32
+    # apply_to_weights on its own weights == oracle
+    new = net.apply_to_weights(net.get_weights())
+    ref = w0[None].copy()
+    oracle.self_apply(do, ref, 1)
+    assert_same_weights(np.concatenate([m.reshape(-1) for m in new]), ref[0])
+    assert [m.shape for m in new] == shapes
+    # self_attack(3)
+    net.self_attack(3)
+    ref = w0[None].copy()
+    oracle.self_apply(do, ref, 3)
+    assert_same_weights(_flat(net), ref[0])
+    # attack / fuck / meet between two nets
+    a, v = mk(network), mk(network)
+    wa, wv = _flat(a), _flat(v)
+    both = np.stack([wa, wv])
+    a.meet(v)
+    assert_same_weights(_flat(v), wv)                                 # meet has no lasting effect
+    assert a.attack(v) is a
+    oracle.apply(do, both, [0], both, [1], both, [1], 1)
+    assert_same_weights(_flat(v), both[1])
+    a.fuck(v)
+    oracle.apply(do, both, [0], both, [1], both, [0], 1)
+    assert_same_weights(_flat(a), both[0])
+    # predicates vs oracle flags
+    for n_ in (net, a, v):
+        fl = oracle.predicates(do, _flat(n_)[None].copy(), 1e-4)[0]
+        n_.with_params(epsilon=1e-4)
+        assert n_.is_diverged() == bool(fl & 1) and n_.is_zero() == bool(fl & 2)
+        assert n_.is_fixpoint() == bool(fl & 4) and n_.is_fixpoint(2) == bool(fl & 8)
+    # set_weights round trip
+    net.set_weights([np.full(s, 0.25, np.float32) for s in shapes])
+    assert (_flat(net) == 0.25).all()
+
+
+def test_weightwise_points_and_apply(api):
+    network, _, _ = api
+    net = network.WeightwiseNeuralNetwork(2, 2)
+    pts, normal = net.compute_all_duplex_weight_points(net.get_weights())
+    assert len(pts) == 14 and normal[2][1:] == [0.0, 1.0 / 3.0, 0.0] and normal[13][1:] == [1.0, 1.0, 0.0]
+    x, y = net.compute_samples()
+    assert x.shape == (14, 4) and y.shape == (14,)
+    out = net.apply(*normal[5])
+    ref = oracle.forward(oracle.ww(), net.get_weights_flat()[None].copy(), np.asarray([normal[5]], np.float32))
+    assert np.float32(out) == ref[0, 0]
+    assert network.WeightwiseNeuralNetwork.normalize_id(1, 3) == 1.0 / 3.0
+    assert network.WeightwiseNeuralNetwork.normalize_id(1, 1) == 1.0
+
+
+def test_identity_fixpoint_and_variation_script(api):
+    """known-fixpoint-variation.py in miniature: the identity fixpoint, perturbed with soup.prng()."""
+    network, soup, _ = api
+    fix = [np.array([[1.0, 0.0], [0.0, 0.0], [0.0, 0.0], [0.0, 0.0]], dtype=np.float32),
+           np.array([[1.0, 0.0], [0.0, 0.0]], dtype=np.float32), np.array([[1.0], [0.0]], dtype=np.float32)]
+    net = network.WeightwiseNeuralNetwork(width=2, depth=2).with_keras_params(activation='sigmoid')
+    net.set_weights(fix)
+    net = network.ParticleDecorator(net.with_params(epsilon=1e-4))
+    assert net.is_fixpoint() and not net.is_zero() and not net.is_diverged()
+    net.self_attack()
+    assert_same_weights(net.get_weights_flat(), np.concatenate([m.reshape(-1) for m in fix]))
+    varied = network.copy.deepcopy(fix)
+    for layer in varied:
+        for cell in layer:
+            for j in range(len(cell)):
+                cell[j] = cell[j] + soup.prng() * 1e-3 if soup.prng() < 0.5 else cell[j] - soup.prng() * 1e-3
+    net.set_weights(varied)
+    steps = 0
+    for _ in range(100):
+        net.self_attack()
+        if net.is_zero() or net.is_diverged():
+            break
+        steps += 1
+    assert 3 <= steps < 100
+
+
+def test_run_net_and_count_like_network_trajectorys(api, golden_dir, tmp_path, monkeypatch):
+    """network_trajectorys.py on the 20 golden initial nets: FixpointExperiment.run_net(net, 100, run_id) logs the
+    same states as the reference's dill and counts {11 divergent, 9 fix_zero}."""
+    network, _, experiment = api
+    monkeypatch.chdir(tmp_path)
+    g = np.load(os.path.join(golden_dir, "ww_self_application.npz"))
+    W, P = g["weights"], g["particle"]
+    with experiment.FixpointExperiment(name="weightwise_self_application") as exp:
+        for run_id, u in enumerate(np.unique(P)):
+            net = network.ParticleDecorator(network.WeightwiseNeuralNetwork(width=2, depth=2)
+                                            .with_keras_params(activation='linear'))
+            net.set_weights(network._split(W[P == u][0], [(4, 2), (2, 2), (2, 1)]))
+            net.states[0]['weights'] = net.get_weights_flat()
+            exp.run_net(net, 100, run_id=run_id + 1)
+            exp.historical_particles[run_id] = net
+            network.K.clear_session()
+        exp.log(exp.counters)
+        exp.save(trajectorys=exp.without_particles())
+    assert exp.counters == dict(divergent=11, fix_zero=9, fix_other=0, fix_sec=0, other=0)
+    for run_id, u in enumerate(np.unique(P)):
+        S = W[P == u]
+        states = exp.historical_particles[run_id].states
+        assert len(states) == len(S)
+        for s, st in enumerate(states):
+            assert_same_weights(st['weights'], S[s])
+            assert st['time'] == s
+    back = experiment.Experiment.from_dill(os.path.join(exp.dir, "trajectorys.dill"))
+    assert len(back.historical_particles) == 20 and os.path.exists(os.path.join(exp.dir, "log.txt"))
+
+
+def test_training_decorator_both_stackings(api):
+    """training-fixpoints.py stacks Training(Particle(net)); soup.py stacks Particle(Training(net))."""
+    network, _, _ = api
+    np.random.seed(3)
+    net = network.TrainingNeuralNetworkDecorator(network.ParticleDecorator(network.WeightwiseNeuralNetwork(2, 2)))
+    net = net.with_params(epsilon=1e-4)
+    w0 = net.get_weights_flat()
+    np.random.seed(3)
+    perm = np.random.permutation(14).astype(np.uint8)[None]
+    np.random.seed(3)
+    loss = net.compiled().train(epoch=1)
+    ref = w0[None].copy()
+    rl = oracle.train(oracle.ww(), ref, 1, perm_mode=1, perm=perm)
+    assert_same_weights(net.get_weights_flat(), ref[0])
+    assert loss == rl[0]
+    assert net.states[-1]['action'] == 'train_self' and net.states[-1]['time'] == 2
+    for e in range(300):
+        net.train(epoch=e + 2, store_states=False)
+    assert net.is_fixpoint() and not net.is_zero()                     # WW trains to a non-trivial fixpoint
+    # the other stacking + learn_from
+    a = network.ParticleDecorator(network.TrainingNeuralNetworkDecorator(network.WeightwiseNeuralNetwork(2, 2)))
+    b = network.ParticleDecorator(network.TrainingNeuralNetworkDecorator(network.WeightwiseNeuralNetwork(2, 2)))
+    wa, wb = a.get_weights_flat(), b.get_weights_flat()
+    np.random.seed(9)
+    perm = np.random.permutation(14).astype(np.uint8)[None]
+    np.random.seed(9)
+    la = a.learn_from(b)
+    ref = wa[None].copy()
+    rl = oracle.train(oracle.ww(), ref, 1, perm_mode=1, perm=perm, teacher_w=wb[None].copy())
+    assert_same_weights(a.get_weights_flat(), ref[0]) and la == rl[0]
+    assert_same_weights(b.get_weights_flat(), wb)
+    with pytest.raises(NotImplementedError):
+        network.TrainingNeuralNetworkDecorator(network.WeightwiseNeuralNetwork(2, 2)).with_compile_params(
+            optimizer='adam').compiled()
+    # AGG and RNN train (one sample per epoch)
+    for mk, do in ((lambda: network.AggregatingNeuralNetwork(4, 2, 2), oracle.agg()),
+                   (lambda: network.RecurrentNeuralNetwork(2, 2), oracle.rnn())):
+        t = network.TrainingNeuralNetworkDecorator(mk())
+        w = t.get_weights_flat()
+        l = t.train(store_states=False)
+        ref = w[None].copy()
+        rl = oracle.train(do, ref, 1)
+        assert_same_weights(t.get_weights_flat(), ref[0])
+        assert l == rl[0] or (np.isnan(l) and np.isnan(rl[0]))
+
+
+def test_aggregating_hooks_and_helpers(api):
+    network, _, _ = api
+    A = network.AggregatingNeuralNetwork
+    assert A.aggregate_average([1, 2, 3, 6]) == 3.0 and A.aggregate_max([1, 5, 2]) == 5
+    assert A.deaggregate_identically(2.0, 3) == [2.0, 2.0, 2.0]
+    net = A(aggregates=4, width=2, depth=2)
+    cols, left = net.get_collected_weights()
+    assert [len(c) for c in cols] == [5, 5, 5, 5] and left == 0
+    aggs, _ = net.get_aggregated_weights()
+    x, y = net.compute_samples()
+    assert x[0].shape == (1, 4) and np.allclose(x[0][0], aggs)
+    # a params hook (aggregate_max) takes the host-hook path around the device forward pass
+    hooked = A(aggregates=4, width=2, depth=2, aggregator=A.aggregate_max)
+    w = hooked.get_weights()
+    new = hooked.apply_to_weights(w)
+    flat = np.concatenate([m.reshape(-1) for m in w])
+    maxes = np.array([flat[i * 5:(i + 1) * 5].max() for i in range(4)], np.float32)
+    out = oracle.forward(oracle.agg(), flat[None].copy(), maxes[None])
+    assert_same_weights(np.concatenate([np.asarray(m, np.float32).reshape(-1) for m in new]), np.repeat(out[0], 5))
+    hooked.self_attack()
+    assert_same_weights(hooked.get_weights_flat(), np.repeat(out[0], 5))
+    ok = net.is_fixpoint_after_aggregation(epsilon=1e-4)
+    assert ok is False or isinstance(ok, tuple)
+    with pytest.raises(NotImplementedError):
+        network.FFTNeuralNetwork(4, 2, 2)
+
+
+def _soup_oracle_replay(soup_mod, network, n, params, gens, okey, seed):
+    """Run a facade Soup and replay the same events through the oracle's exact-order generation."""
+    import random
+    do = oracle.desc(*okey[:3], okey[3])
+    random.seed(seed)
+    np.random.seed(seed)
+    mk = {0: lambda: network.WeightwiseNeuralNetwork(2, 2), 1: lambda: network.AggregatingNeuralNetwork(4, 2, 2),
+          2: lambda: network.RecurrentNeuralNetwork(2, 2)}[okey[0]]
+    gen = lambda: network.TrainingNeuralNetworkDecorator(mk()).with_params(epsilon=1e-4)  # noqa: E731
+    s = soup_mod.Soup(n, gen, **params)
+    s.seed()
+    ref = np.stack([p.get_weights_flat() for p in s.particles])
+    state = random.getstate()
+    for g in range(1, gens + 1):
+        # the draws the Soup will make this generation
+        random.setstate(state)
+        att, lrn = np.full(n, -1), np.full(n, -1)
+        for i in range(n):
+            if random.random() < params.get('attacking_rate', 0.1):
+                att[i] = int(random.random() * n)
+            if random.random() < params.get('learn_from_rate', 0.1):
+                lrn[i] = int(random.random() * n)
+        random.setstate(state)
+        culls = params.get('remove_divergent') or params.get('remove_zero')
+        spares_before = None
+        if culls:
+            s._top_up_spares(n)
+            spares_before = np.stack([network._base(x).get_weights_flat() for x in s._spares[:n]])
+        s.evolve()
+        state = random.getstate()
+        po = oracle.soup_params(attacking_rate=params.get('attacking_rate', 0.1),
+                                learn_from_rate=params.get('learn_from_rate', 0.1), train=params.get('train', 0),
+                                learn_from_severity=params.get('learn_from_severity', 1),
+                                remove_divergent=params.get('remove_divergent', False),
+                                remove_zero=params.get('remove_zero', False), epsilon=1e-4, perm_mode=2)
+        res = oracle.soup_ordered(do, po, ref, att, lrn, seed=network._EngineState.seed ^ 0x5eed50, gen=g,
+                                  spares=spares_before)
+        got = np.stack([p.get_weights_flat() for p in s.particles])
+        assert_same_weights(got, ref, "generation %d" % g)
+    return s
+
+
+@pytest.mark.parametrize("okey", [(0, 2, 2, 0), (1, 2, 2, 4), (2, 2, 2, 0)])
+def test_soup_evolve_exact_order(api, okey):
+    """soup_trajectorys.py / mixed-soup.py style soups: Soup.evolve == the oracle's exact-order generation, with
+    culling, respawn from generator(), uids and the state log schema."""
+    network, soup_mod, _ = api
+    params = dict(attacking_rate=0.3, learn_from_rate=0.2, train=3, learn_from_severity=2, remove_divergent=True,
+                  remove_zero=True)
+    uid0 = network.ParticleDecorator.next_uid
+    s = _soup_oracle_replay(soup_mod, network, 20, params, 8, okey, seed=5)
+    assert s.time == 8 and len(s.particles) == 20
+    assert set(s.historical_particles) >= {p.get_uid() for p in s.particles}
+    assert min(s.historical_particles) == uid0
+    for uid, p in s.historical_particles.items():
+        assert p.states[0]['action'] == 'init' and p.states[0]['time'] == 0
+        for st in p.states[1:]:
+            assert set(st) >= {'class', 'weights', 'time', 'action', 'counterpart'} and np.isfinite(st['weights']).all()
+            assert st['action'] in ('attacking', 'learn_from', 'train_self', 'divergent_dead', 'zweo_dead')
+            if st['action'] == 'train_self':
+                assert st['fitted'] == 3 and st['counterpart'] is None and np.isfinite(st['loss'])
+    dead = [st for p in s.historical_particles.values() for st in p.states if st['action'].endswith('_dead')]
+    for st in dead:
+        assert st['counterpart'] in s.historical_particles
+    counts = s.count()
+    assert sum(counts.values()) == 20
+    slim = s.without_particles()
+    assert all(isinstance(v, list) for v in slim.historical_particles.values())
+
+
+def test_soup_training_finds_fixpoints(api):
+    """soup_trajectorys.py: 20 WW particles, train=30, attack 0.1, cull: after 100 generations the reference logs
+    {fix_other: 13, other: 7}; require the same qualitative outcome (mostly non-trivial fixpoints, nothing dead)."""
+    import random
+    network, soup_mod, _ = api
+    random.seed(1)
+    gen = lambda: network.TrainingNeuralNetworkDecorator(network.WeightwiseNeuralNetwork(2, 2)) \
+        .with_keras_params(activation='linear').with_params(epsilon=0.0001)  # noqa: E731
+    s = soup_mod.Soup(20, gen).with_params(remove_divergent=True, remove_zero=True, train=30, learn_from_rate=-1)
+    s.seed()
+    for _ in range(100):
+        s.evolve()
+    c = s.count()
+    assert c['divergent'] == 0 and c['fix_zero'] == 0 and c['fix_other'] >= 8, c
+    some = next(iter(s.historical_particles.values()))
+    assert some.states[-1]['fitted'] == 30 and some.states[-1]['loss'] < 1e-3
+
+
+def test_population_soup_single_rank(api):
+    """PopulationSoup (snapshot-synchronous, device-only): equals the oracle's sync generations bit-for-bit."""
+    network, soup_mod, _ = api
+    import srnn_engine as eng
+    n = 5000
+    ps = soup_mod.PopulationSoup(eng.KIND_WW, n, seed=77, attacking_rate=0.1, learn_from_rate=0.1, train=1,
+                                 remove_divergent=True, remove_zero=True, epsilon=1e-4)
+    ps.track_uids = True
+    ps.seed_particles()
+    ref = ps.local.numpy().copy()
+    do = oracle.ww()
+    po = oracle.soup_params(attacking_rate=0.1, learn_from_rate=0.1, train=1, learn_from_severity=1,
+                            remove_divergent=True, remove_zero=True, epsilon=1e-4, perm_mode=2)
+    for g in range(1, 6):
+        ps.evolve()
+        out = np.zeros_like(ref)
+        oracle.soup_sync(do, po, ref, n, out, 0, n, 77, g)
+        ref = out
+        assert_same_weights(ps.local.numpy(), ref, "generation %d" % g)
+    c = ps.count()
+    rc = oracle.classify(do, ref, 1e-4)[1]
+    assert list(c.values()) == rc.tolist()
+    assert ps.next_uid >= n and int(ps.uid.max().item()) == ps.next_uid - 1
