@@ -131,6 +131,21 @@ int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const floa
 int srnn_assign_uids(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *uid, int64_t *block_tmp,
                      int64_t *n_dead_out, void *stream);
 
+/* Same result as srnn_assign_uids, for callers that cannot allocate device memory.  (No counterpart in the
+ * reference: it exists for hosts that only pass through device pointers owned by another runtime and link no
+ * allocator themselves, and for soup loops whose device memory was handed out once at start-up and that must
+ * not call cudaMalloc -- which synchronises the whole device -- between generations.)  The block-count scratch
+ * is a fixed array inside the library image: 128 KiB on every GPU that loads libsrnn_b200.so, kept until the
+ * process exits.  n may be at most SRNN_UIDS_STATIC_MAX; larger n is refused with SRNN_ERR_LIMIT.  The call
+ * makes no allocation of any kind.  The first call on a device looks up the array's device address (a host-side
+ * query with that device current); make that first call before starting any stream capture.  All calls share
+ * the one array per GPU: it needs no clearing between calls (every counter is rewritten before it is read),
+ * but two calls whose kernels overlap on the same GPU -- different streams or different host threads --
+ * race on it, so keep these calls ordered on one stream per device. */
+#define SRNN_UIDS_STATIC_MAX (1 << 24)
+int srnn_assign_uids_static(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *uid, int64_t *n_dead_out,
+                            void *stream);
+
 /* FP32 issue-rate probe: an FFMA-only kernel (independent chains, operands in registers) used as the
  * measured roofline denominator for the register-resident kernels (MEASURED_PEAKS.json has no FP32 entry).
  * Runs `iters` x 64 FFMA per thread over grid x block threads; out = float[grid*block] sink. */

@@ -16,6 +16,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 
 #include "../../include/srnn_b200.h"
 #include "srnn_device.cuh"
@@ -885,6 +886,56 @@ int srnn_assign_uids(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *
     uid_blockscan_kernel<<<1, SCAN_BS, 0, (cudaStream_t)stream>>>(block_tmp, nb, n_dead_out);
     uid_assign_kernel<<<(unsigned)nb, SCAN_BS, 0, (cudaStream_t)stream>>>(dead, n, uid_base, block_tmp, uid);
     return check_launch("srnn_assign_uids");
+}
+
+// ---- allocation-free variant of srnn_assign_uids ------------------------------------------------------------
+// Some hosts of this library only ever hold device pointers that somebody else allocated: a ctypes / cgo style
+// binding that passes through arenas owned by another framework and links no CUDA allocator of its own, or a
+// soup loop whose device memory was carved up once at start-up (a population sized to fill HBM) and which must
+// not touch cudaMalloc -- with its implicit device-wide synchronisation -- between generations.  For them the
+// block-count scratch of the uid prefix sum lives inside the library image: one fixed array per GPU that
+// loads libsrnn_b200.so, SRNN_UIDS_STATIC_MAX / 1024 + 1 counters = 128 KiB, held until the process exits.
+static __device__ __align__(256) long long g_uid_scratch[SRNN_UIDS_STATIC_MAX / srnn::SCAN_BS + 1];
+
+// In host code `g_uid_scratch` is only a handle for the symbol, not an address a kernel may use; the device
+// address is looked up once per device (with that device current) and cached.
+static int uid_scratch_of_current_device(int64_t **out) {
+    constexpr int MAX_DEV = 64;
+    static int64_t *cached[MAX_DEV] = {};
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return srnn::fail(SRNN_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= MAX_DEV) return srnn::fail(SRNN_ERR_LIMIT, "device ordinal beyond the static-scratch table%s");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_uid_scratch);
+        if (e != cudaSuccess || !p)
+            return srnn::fail(SRNN_ERR_CUDA, "cudaGetSymbolAddress(g_uid_scratch): %s", cudaGetErrorString(e));
+        cached[dev] = static_cast<int64_t *>(p);
+    }
+    *out = cached[dev];
+    return SRNN_OK;
+}
+
+int srnn_assign_uids_static(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *uid, int64_t *n_dead_out,
+                            void *stream) {
+    if (!dead || !uid) return fail(SRNN_ERR_ARG, "dead or uid is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    if (n > (int64_t)SRNN_UIDS_STATIC_MAX)
+        return fail(SRNN_ERR_LIMIT, "srnn_assign_uids_static: n exceeds SRNN_UIDS_STATIC_MAX (2^24 particles); "
+                                    "use srnn_assign_uids with caller-provided scratch%s");
+    int64_t *scratch = nullptr;
+    int rc = uid_scratch_of_current_device(&scratch);   // first call on a device resolves the symbol address
+    if (rc) return rc;
+    // Nothing in the scratch has to start from zero: every counter that is read was written earlier in this
+    // same call (counts -> scan -> offsets), so whatever an earlier call left behind is never observed.
+    const int64_t nb = (n + SCAN_BS - 1) / SCAN_BS;
+    uid_count_kernel<<<(unsigned)nb, SCAN_BS, 0, (cudaStream_t)stream>>>(dead, n, scratch);
+    uid_blockscan_kernel<<<1, SCAN_BS, 0, (cudaStream_t)stream>>>(scratch, nb, n_dead_out);
+    uid_assign_kernel<<<(unsigned)nb, SCAN_BS, 0, (cudaStream_t)stream>>>(dead, n, uid_base, scratch, uid);
+    return check_launch("srnn_assign_uids_static");
 }
 
 int srnn_fp32_probe(float *out, int32_t grid, int32_t block, int32_t iters, void *stream) {

@@ -28,7 +28,8 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_sync", "srnn_assign_uids", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_sync", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+UIDS_STATIC_MAX = 1 << 24
 
 
 class NetDesc(C.Structure):
@@ -280,6 +281,14 @@ def soup_sync(desc, params, snap, n_total, w_out, slot0, n, seed, gen, scratch, 
 def assign_uids(dead, uid, uid_base, block_tmp, n_dead_out=None):
     _chk(lib().srnn_assign_uids(_ptr(dead), C.c_int64(dead.numel()), C.c_int64(uid_base), _ptr(uid), _ptr(block_tmp),
                                 _ptr(n_dead_out), _stream()))
+
+
+def assign_uids_static(dead, uid, uid_base, n_dead_out=None, n=None):
+    """srnn_assign_uids without caller scratch: for hosts that cannot allocate device memory (they pass through
+    pointers owned by someone else, or their memory was fixed at start-up).  At most UIDS_STATIC_MAX particles;
+    calls on one GPU must not overlap (they share one array inside the library)."""
+    _chk(lib().srnn_assign_uids_static(_ptr(dead), C.c_int64(dead.numel() if n is None else n), C.c_int64(uid_base),
+                                       _ptr(uid), _ptr(n_dead_out), _stream()))
 
 
 def kfv(desc, base, n, scale, level, max_steps, eps, seed, slot0=0, want_times=True, want_hist=True,
