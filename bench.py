@@ -138,6 +138,82 @@ def run_reference(args, rank):
                 "(same arithmetic, SIMD + OpenMP over nets)"}), flush=True)
 
 
+def _timed(torch, fn, reps=1):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) * 1e-3 / reps
+
+
+def secondary_legs(eng, torch, dist, rank, world, dev):
+    """The other half of BASELINE.json's metric (soup generations/s) and the self-training config, device-timed.
+    Reported as extra keys of the JSON line; the headline `value` stays net self-applications/s."""
+    from soup import PopulationSoup
+    out = {}
+
+    def sync_max(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    if world == 1:
+        # configs[2]: soup of 100k WW, attack 0.1 + self-train 1 epoch, respawn of divergent / zero nets, 1000 generations
+        kw = dict(attacking_rate=0.1, learn_from_rate=-1, train=1, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+        s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, **kw).seed_particles()
+        s.evolve(50)
+        dt = _timed(torch, lambda: s.evolve(1000))
+        out["soup"] = {"metric": "soup generations/sec", "value": 1000 / dt, "unit": "generations/s",
+                       "config": dict(workload="soup_100k_ww", particles=100_000, generations=1000, mode="snapshot-synchronous", **kw),
+                       "particle_generations_per_s": 100_000 * 1000 / dt, "classes_after": s.count()}
+        # same soup at 10M particles, train=0 (configs[3]'s per-GPU regime): one HBM pass per generation
+        kw0 = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+        s = PopulationSoup(eng.KIND_WW, 10_000_000, seed=4, **kw0).seed_particles()
+        s.evolve(4)
+        dt = _timed(torch, lambda: s.evolve(20))
+        out["soup_10m"] = {"metric": "soup generations/sec", "value": 20 / dt, "unit": "generations/s",
+                           "config": dict(workload="soup_10m_ww_train0", particles=10_000_000, generations=20, **kw0),
+                           "hbm_gbs_algorithmic": 10_000_000 * 130.0 * 20 / dt / 1e9}
+        del s
+        # configs[1]: self-training, 10k WW + 10k AGG(4) x 1000 epochs; and a 2^20-net WW run for throughput
+        dw, da = eng.make_desc(eng.KIND_WW, 2, 2), eng.make_desc(eng.KIND_AGG, 2, 2, 4)
+        pw, pa = eng.Population(dw, 10_000).init(seed=1), eng.Population(da, 10_000).init(seed=1)
+        pw.train(10, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False)
+        dt = _timed(torch, lambda: (pw.train(1000, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False),
+                                    pa.train(1000, want_loss=False)))
+        big = eng.Population(dw, 1 << 20).init(seed=5)
+        big.train(2, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False)
+        dtb = _timed(torch, lambda: big.train(100, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False))
+        out["self_train"] = {"metric": "net self-train epochs/sec", "config_10k_ww_10k_agg_1000_epochs_s": dt,
+                             "value": (1 << 20) * 100 / dtb, "unit": "epochs/s",
+                             "config": {"workload": "ww22_self_train", "nets": 1 << 20, "epochs": 100, "perm": "philox"},
+                             "tflops_algorithmic": (1 << 20) * 100 * 1148.0 / dtb / 1e12,
+                             "classes_10k_ww": dict(zip(eng.CLS_NAMES, pw.classify(1e-4)[1].cpu().tolist()))}
+    else:
+        # configs[3]: mixed soup of 10M nets (one third each WW / AGG / RNN, partners within kind), learn_from + attack,
+        # sharded by particle index over the ranks with one all-gather of the record arena per generation
+        third = (10_000_000 // 3) // world * world
+        kw = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, epsilon=1e-4)
+        soups = [PopulationSoup(k, third, aggregates=a, seed=5 + k, **kw).seed_particles()
+                 for k, a in ((eng.KIND_WW, 0), (eng.KIND_AGG, 4), (eng.KIND_RNN, 0))]
+        for s in soups:
+            s.evolve(2)
+        if world > 1:
+            dist.barrier()
+        gens = 20
+        dt = sync_max(_timed(torch, lambda: [s.evolve(1) for s in soups], reps=gens))
+        gathered = sum(s.size * s.desc.n_weights * 4 for s in soups)
+        out["soup"] = {"metric": "soup generations/sec", "value": 1.0 / dt, "unit": "generations/s",
+                       "config": dict(workload="mixed_soup_10m_sharded", particles=3 * third, kinds="WW/AGG/RNN thirds",
+                                      ranks=world, generations=gens, exchange="all-gather of record arenas per generation", **kw),
+                       "allgather_bytes_per_generation_per_gpu": gathered, "allgather_gbs_if_all_time": gathered / dt / 1e9}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -244,6 +320,8 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * n * N_STEPS * K / t.item()
 
+    extra = secondary_legs(eng, torch, dist, rank, world, dev)
+
     if rank == 0:
         achieved_tf = FLOP_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / 1e12
         peak_tf = probe * 2.0 / 1e12
@@ -267,6 +345,7 @@ def main():
                          "issue_frac": FP32_INSTR_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / probe,
                          "hbm_gbs": BYTES_PER_NET * n / (kern_ms * 1e-3) / 1e9},
         }
+        line.update(extra)
         if world == 1:
             v, cores, sample = cpu_port_rate(1 << 20, args.cpu_seconds)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}

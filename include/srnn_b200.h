@@ -125,6 +125,14 @@ int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const floa
                    int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed,
                    uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream);
 
+/* n_gens consecutive snapshot-synchronous generations (gen0, gen0+1, ...) of an UNSHARDED soup in one call, so a
+ * small soup is not bound by the host's per-call overhead: generation gen0+g reads w_a and writes w_b for even g,
+ * the other way round for odd g -- the newest arena is w_b if n_gens is odd, else w_a.  Same arguments and
+ * semantics as srnn_soup_sync with n_total = n, slot0 = 0; action / dead (nullable) hold the LAST generation's. */
+int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w_a, float *w_b, int64_t ld, int64_t n,
+                       uint64_t seed, uint64_t gen0, int32_t n_gens, int32_t *scratch, uint8_t *action, uint8_t *dead,
+                       void *stream);
+
 /* ParticleDecorator uid allocation for respawned particles (code/network.py:167-171, soup.py:78,83):
  * uid[i] <- uid_base + (number of dead[j] != 0 with j < i) for every dead i; *n_dead_out (device int64,
  * nullable) receives the total.  block_tmp = int64[ceil(n/1024) + 1] scratch. */

@@ -877,6 +877,19 @@ int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const floa
     return check_launch("srnn_soup_sync");
 }
 
+int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w_a, float *w_b, int64_t ld, int64_t n,
+                       uint64_t seed, uint64_t gen0, int32_t n_gens, int32_t *scratch, uint8_t *action, uint8_t *dead,
+                       void *stream) {
+    if (n_gens < 0) return fail(SRNN_ERR_ARG, "n_gens < 0%s");
+    for (int32_t g = 0; g < n_gens; ++g) {   // generation gen0+g reads one arena and writes the other
+        float *src = (g & 1) ? w_b : w_a, *dst = (g & 1) ? w_a : w_b;
+        int rc = srnn_soup_sync(d, p, src, ld, n, dst, ld, 0, n, seed, gen0 + (uint64_t)g, scratch, action, nullptr, dead,
+                                stream);
+        if (rc) return rc;
+    }
+    return SRNN_OK;
+}
+
 int srnn_assign_uids(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *uid, int64_t *block_tmp,
                      int64_t *n_dead_out, void *stream) {
     if (!dead || !uid || !block_tmp) return fail(SRNN_ERR_ARG, "dead, uid or block_tmp is NULL%s");

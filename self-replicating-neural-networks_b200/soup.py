@@ -268,6 +268,14 @@ class PopulationSoup:
         import torch
         import torch.distributed as dist
         sp = self._soup_params()
+        if self.world == 1 and not self.track_uids and iterations > 1:
+            # unsharded: all generations in one C call (no per-generation host overhead)
+            _eng.soup_sync_run(self.desc, sp, self.local.w, self._next, self.seed, self.time + 1, iterations,
+                               self._scratch, action=self.action, dead=self.dead)
+            self.time += iterations
+            if iterations & 1:
+                self.local.w, self._next = self._next, self.local.w
+            return self
         for _ in range(iterations):
             self.time += 1
             if self.world > 1:

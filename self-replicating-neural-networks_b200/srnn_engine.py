@@ -28,7 +28,7 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_sync", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_sync", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
 UIDS_STATIC_MAX = 1 << 24
 
 
@@ -276,6 +276,13 @@ def soup_sync(desc, params, snap, n_total, w_out, slot0, n, seed, gen, scratch, 
     _chk(lib().srnn_soup_sync(C.byref(desc), C.byref(params), _ptr(snap), C.c_int64(snap.shape[1]), C.c_int64(n_total),
                               _ptr(w_out), C.c_int64(w_out.shape[1]), C.c_int64(slot0), C.c_int64(n), C.c_uint64(seed),
                               C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead), _stream()))
+
+
+def soup_sync_run(desc, params, w_a, w_b, seed, gen0, n_gens, scratch, action=None, dead=None):
+    """n_gens generations of an unsharded soup in ONE call (ping-pong between w_a and w_b; newest = w_b if n_gens odd)."""
+    _chk(lib().srnn_soup_sync_run(C.byref(desc), C.byref(params), _ptr(w_a), _ptr(w_b), C.c_int64(w_a.shape[1]),
+                                  C.c_int64(w_a.shape[0]), C.c_uint64(seed), C.c_uint64(gen0), C.c_int32(n_gens),
+                                  _ptr(scratch), _ptr(action), _ptr(dead), _stream()))
 
 
 def assign_uids(dead, uid, uid_base, block_tmp, n_dead_out=None):
