@@ -213,6 +213,51 @@ class Soup(object):
             print(particle.is_fixpoint())
 
 
+class _CudaBackend:
+    """PopulationSoup's compute backend: the B200 engine.  (Tests inject a CPU stand-in to exercise the sharding
+    logic under gloo without a GPU; the product never uses anything else.)"""
+
+    def __init__(self, device=None):
+        import torch
+        _eng._torch()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+
+    def alloc(self, shape, dtype):
+        import torch
+        return torch.zeros(shape, dtype=dtype, device=self.device)
+
+    def init(self, desc, w, seed, slot0, generation):
+        _eng.Population(desc, w.shape[0], device=self.device, ld=w.shape[1], w=w).init(seed, slot0=slot0, generation=generation)
+
+    def soup_sync(self, desc, sp_kwargs, snap, n_total, w_out, slot0, n, seed, gen, scratch, action, dead):
+        _eng.soup_sync(desc, _eng.make_soup_params(**sp_kwargs), snap, n_total, w_out, slot0, n, seed, gen, scratch,
+                       action=action, dead=dead)
+
+    def soup_sync_run(self, desc, sp_kwargs, w_a, w_b, seed, gen0, n_gens, scratch, action, dead):
+        _eng.soup_sync_run(desc, _eng.make_soup_params(**sp_kwargs), w_a, w_b, seed, gen0, n_gens, scratch,
+                           action=action, dead=dead)
+
+    def classify(self, desc, w, eps, with_fix_sec):
+        return _eng.Population(desc, w.shape[0], device=self.device, ld=w.shape[1], w=w).classify(eps, with_fix_sec)[1]
+
+    def assign_uids(self, dead, uid, base, tmp, n_dead):
+        _eng.assign_uids(dead, uid, base, tmp, n_dead)
+
+
+def shard_of(size, world, rank):
+    """Contiguous block of particle indices owned by `rank`: (slot0, n_local).  Global index = slot0 + local."""
+    if size % world:
+        raise ValueError("population size must be a multiple of the number of ranks")
+    n_local = size // world
+    return rank * n_local, n_local
+
+
+def uid_base_of(rank, dead_counts, next_uid):
+    """First uid handed out on `rank` this generation and the new global counter: respawned particles get uids in
+    global particle order (= the order generate_particle would be called, code/soup.py:78,83)."""
+    return next_uid + int(sum(dead_counts[:rank])), next_uid + int(sum(dead_counts))
+
+
 class PopulationSoup:
     """Population-scale soup of ONE net shape, device-resident, optionally sharded by particle index over the ranks
     of a torch.distributed process group (one rank per GPU).  One generation =
@@ -220,34 +265,39 @@ class PopulationSoup:
     Pairings, SGD sample orders and respawns are Philox functions of (seed, global particle index, generation),
     so the result does not depend on how the population is sharded."""
 
-    def __init__(self, kind, size, width=2, depth=2, aggregates=0, seed=0, group=None, device=None, **params):
+    def __init__(self, kind, size, width=2, depth=2, aggregates=0, seed=0, group=None, device=None, backend=None,
+                 **params):
         import torch
         import torch.distributed as dist
         self.desc = _eng.make_desc(kind, width, depth, aggregates)
         self.group = group
-        self.world = dist.get_world_size(group) if (group is not None or (dist.is_available() and dist.is_initialized())) else 1
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
-        if size % self.world:
-            raise ValueError("population size must be a multiple of the number of ranks")
-        self.size, self.n_local = int(size), int(size) // self.world
-        self.slot0 = self.rank * self.n_local
+        self.size = int(size)
+        self.slot0, self.n_local = shard_of(self.size, self.world, self.rank)
         self.seed, self.time = int(seed), 0
         self.params = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1,
                            remove_divergent=False, remove_zero=False, epsilon=1e-4, perm_mode=_eng.PERM_PHILOX)
         self.params.update(params)
-        self.local = _eng.Population(self.desc, self.n_local, device=device)
-        dev = self.local.device
-        nw = self.desc.n_weights
-        self._snap = torch.zeros((self.size, nw), dtype=torch.float32, device=dev) if self.world > 1 else None
-        self._next = torch.zeros((self.n_local, nw), dtype=torch.float32, device=dev)
-        self._scratch = torch.zeros(self.size + self.n_local, dtype=torch.int32, device=dev)
-        self.dead = torch.zeros(self.n_local, dtype=torch.uint8, device=dev)
-        self.action = torch.zeros(self.n_local, dtype=torch.uint8, device=dev)
-        self.uid = torch.arange(self.slot0, self.slot0 + self.n_local, dtype=torch.int64, device=dev)
-        self._uid_tmp = torch.zeros((self.n_local + 1023) // 1024 + 1, dtype=torch.int64, device=dev)
-        self._n_dead = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.backend = backend or _CudaBackend(device)
+        nw, B = self.desc.n_weights, self.backend
+        self.w = B.alloc((self.n_local, nw), torch.float32)
+        self._next = B.alloc((self.n_local, nw), torch.float32)
+        self._snap = B.alloc((self.size, nw), torch.float32) if self.world > 1 else None
+        self._scratch = B.alloc((self.size + self.n_local,), torch.int32)
+        self.dead = B.alloc((self.n_local,), torch.uint8)
+        self.action = B.alloc((self.n_local,), torch.uint8)
+        self.uid = B.alloc((self.n_local,), torch.int64)
+        self.uid.copy_(torch.arange(self.slot0, self.slot0 + self.n_local, dtype=torch.int64))
+        self._uid_tmp = B.alloc(((self.n_local + 1023) // 1024 + 1,), torch.int64)
+        self._n_dead = B.alloc((1,), torch.int64)
         self.next_uid = self.size
         self.track_uids = False
+
+    @property
+    def local(self):
+        """The local slice as an engine Population (CUDA backend only)."""
+        return _eng.Population(self.desc, self.n_local, device=self.w.device, ld=self.w.shape[1], w=self.w)
 
     def with_params(self, **kwargs):
         self.params.update(kwargs)
@@ -255,60 +305,56 @@ class PopulationSoup:
 
     def seed_particles(self):
         """Soup.seed: fresh Keras-style nets for every local particle."""
-        self.local.init(self.seed, slot0=self.slot0, generation=0)
+        self.backend.init(self.desc, self.w, self.seed, self.slot0, 0)
         return self
 
-    def _soup_params(self):
-        p = self.params
-        return _eng.make_soup_params(**{k: p[k] for k in ("attacking_rate", "learn_from_rate", "train",
-                                                          "learn_from_severity", "remove_divergent", "remove_zero",
-                                                          "epsilon", "perm_mode")})
+    def _sp(self):
+        return {k: self.params[k] for k in ("attacking_rate", "learn_from_rate", "train", "learn_from_severity",
+                                            "remove_divergent", "remove_zero", "epsilon", "perm_mode")}
 
     def evolve(self, iterations=1):
-        import torch
         import torch.distributed as dist
-        sp = self._soup_params()
-        if self.world == 1 and not self.track_uids and iterations > 1:
+        sp, B = self._sp(), self.backend
+        if self.world == 1 and not self.track_uids and iterations > 1 and hasattr(B, "soup_sync_run"):
             # unsharded: all generations in one C call (no per-generation host overhead)
-            _eng.soup_sync_run(self.desc, sp, self.local.w, self._next, self.seed, self.time + 1, iterations,
-                               self._scratch, action=self.action, dead=self.dead)
+            B.soup_sync_run(self.desc, sp, self.w, self._next, self.seed, self.time + 1, iterations, self._scratch,
+                            self.action, self.dead)
             self.time += iterations
             if iterations & 1:
-                self.local.w, self._next = self._next, self.local.w
+                self.w, self._next = self._next, self.w
             return self
         for _ in range(iterations):
             self.time += 1
             if self.world > 1:
-                dist.all_gather_into_tensor(self._snap, self.local.w, group=self.group)   # NCCL over NVLink
+                dist.all_gather_into_tensor(self._snap, self.w, group=self.group)   # NCCL over NVLink on the box
                 snap = self._snap
             else:
-                snap = self.local.w
-            _eng.soup_sync(self.desc, sp, snap, self.size, self._next, self.slot0, self.n_local, self.seed, self.time,
-                           self._scratch, action=self.action, dead=self.dead)
-            self.local.w, self._next = self._next, self.local.w
+                snap = self.w
+            B.soup_sync(self.desc, sp, snap, self.size, self._next, self.slot0, self.n_local, self.seed, self.time,
+                        self._scratch, self.action, self.dead)
+            self.w, self._next = self._next, self.w
             if self.track_uids:
                 self._assign_uids()
         return self
 
     def _assign_uids(self):
-        """Deterministic global uids for respawned particles: rank offsets by an all-gather of the per-rank counts."""
+        """Deterministic global uids for respawned particles: rank offsets from an all-gather of per-rank counts."""
         import torch
         import torch.distributed as dist
+        mine = self.dead.sum(dtype=torch.int64).reshape(1)
         if self.world > 1:
-            counts = torch.zeros(self.world, dtype=torch.int64, device=self.local.device)
-            mine = self.dead.sum(dtype=torch.int64).reshape(1)
+            counts = torch.zeros(self.world, dtype=torch.int64, device=mine.device)
             dist.all_gather_into_tensor(counts, mine, group=self.group)
-            c = counts.cpu()
-            base, total = self.next_uid + int(c[:self.rank].sum()), int(c.sum())
+            counts = counts.cpu().tolist()
         else:
-            base, total = self.next_uid, None
-        _eng.assign_uids(self.dead, self.uid, base, self._uid_tmp, self._n_dead)
-        self.next_uid += int(self._n_dead.item()) if total is None else total
+            counts = [int(mine.item())]
+        base, self.next_uid = uid_base_of(self.rank, counts, self.next_uid)
+        self.backend.assign_uids(self.dead, self.uid, base, self._uid_tmp, self._n_dead)
 
     def count(self, with_fix_sec=True):
         """Soup.count over the whole (possibly sharded) population."""
         import torch.distributed as dist
-        _, cnt = self.local.classify(self.params["epsilon"], with_fix_sec=with_fix_sec)
+        cnt = self.backend.classify(self.desc, self.w, self.params["epsilon"], with_fix_sec)
         if self.world > 1:
             dist.all_reduce(cnt, group=self.group)
         return dict(zip(_eng.CLS_NAMES, (int(c) for c in cnt.cpu().numpy())))
