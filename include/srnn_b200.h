@@ -119,11 +119,24 @@ int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *
  * per-generation all-gather when sharded); this call owns particles [slot0, slot0+n) and writes their
  * new records to w_out (w_out must not alias snap).  Pairings are Philox draws of (seed, slot, gen) in the
  * reference's per-particle order; a victim hit several times applies attackers in ascending index.
- *   scratch  int32[n_total + n]: attack lists (head[n] + next[n_total]); contents need no initialisation
+ *   scratch  int32[n_total + 4*n + 16]: attack lists (head[n] | next[n_total]) and, for the multi-pass path taken
+ *            by large soups, compacted victim / learner work lists, flags and counters; needs no initialisation
  *   action (nullable) uint8[n], loss (nullable) double[n], dead (nullable) uint8[n] (1 = respawned) */
 int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const float *snap, int64_t snap_ld,
                    int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed,
                    uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream);
+
+/* Soup.evolve, snapshot-synchronous generation of a SHARDED soup without a gather: the exchange step is fused
+ * into the generation kernel.  shards (HOST array of n_shards DEVICE pointers) are the ranks' start-of-generation
+ * arenas, each holding shard_len particles (rank r owns global particles [r*shard_len, (r+1)*shard_len)); peers'
+ * arenas must be mapped into this process (CUDA peer / symmetric memory over NVLink).  The kernel reads its own
+ * records from shards[my_shard] and fetches only the partner records it needs (attackers, teachers: ~20 % of the
+ * particles) straight from the owning GPU.  Everything else as srnn_soup_sync with n = shard_len.  The caller
+ * must order generations across ranks (a barrier after each one) and ping-pong arenas: w_out of generation g is
+ * the shard of generation g+1. */
+int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, const float *const *shards, int32_t n_shards,
+                         int64_t shard_len, int32_t my_shard, int64_t ld, float *w_out, int64_t out_ld, uint64_t seed,
+                         uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream);
 
 /* n_gens consecutive snapshot-synchronous generations (gen0, gen0+1, ...) of an UNSHARDED soup in one call, so a
  * small soup is not bound by the host's per-call overhead: generation gen0+g reads w_a and writes w_b for even g,

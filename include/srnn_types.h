@@ -64,11 +64,13 @@ typedef struct srnn_soup_params {
     double  epsilon;             /* particles' params['epsilon']                  */
     float   lr;                  /* Keras SGD default 0.01                        */
     int32_t perm_mode;           /* SRNN_PERM_NONE or SRNN_PERM_PHILOX            */
+    int32_t engine_path;         /* srnn_soup_sync only: 0 auto, 1 fused single kernel, 2 multi-pass (same results) */
 } srnn_soup_params;
 
 #define SRNN_MAX_WEIGHTS 64      /* per-net weight count supported by the generic code paths */
 #define SRNN_MAX_WIDTH 8
 #define SRNN_MAX_LAYERS 8
+#define SRNN_MAX_SHARDS 16       /* ranks whose arenas one soup generation can read directly (peer memory) */
 
 /* status codes (0 = ok); NaN/Inf in the data is never an error */
 enum { SRNN_OK = 0, SRNN_ERR_ARG = 1, SRNN_ERR_SHAPE = 2, SRNN_ERR_CUDA = 3, SRNN_ERR_LIMIT = 4 };

@@ -24,6 +24,17 @@
 namespace srnn {
 
 constexpr int BS = 256;  // threads per CTA = records per tile
+#ifndef SRNN_SOUP_BS
+#define SRNN_SOUP_BS 128
+#endif
+// CTA size / minimum resident CTAs of the fused soup generation kernel.  The kernel is latency-bound on its short
+// serial phases (one warp per CTA walking attack lists or running a learner's SGD while the others wait at the
+// barrier), so it wants many resident CTAs: A/B on a B200 at 10 M particles, ms per generation (train = 0 / 1):
+// 256 thr x>=1: 0.93 / 1.38;  128 x>=1: 0.98 / 1.45;  64 x>=1: 1.11 / 1.66;  256 x>=6: 0.79 / 1.24;  128 x>=10: 0.73 / 1.18.
+constexpr int SOUP_BS = SRNN_SOUP_BS;
+// engine_path = 0 (auto) takes the fused single kernel; the multi-pass (globally compacted) generation is kept
+// selectable (engine_path = 2): it measured 0.91 / 1.33 ms against 0.73 / 1.18 ms for the fused kernel at 10 M particles.
+constexpr int64_t SOUP_MULTIPASS_MIN = INT64_MAX;
 
 // ------------------------------------------------------------------------------------------------ errors
 static thread_local char g_err[512] = "";
@@ -53,47 +64,100 @@ static int make_eps(double eps, Eps *e) {
 }
 
 // ------------------------------------------------------------------------------------------------ tile staging
-// Shared-memory record stride is NW|1 (odd) so the per-thread reads are bank-conflict free.
-template <int NW> __host__ __device__ constexpr int tile_stride() { return NW | 1; }
+// A CTA's tile = NT consecutive records = one contiguous run of NT*NW floats in a packed arena.  It moves between HBM
+// and shared memory as a flat copy (16-byte vectors when the run is 16-byte aligned) -- no per-element index maths --
+// and each thread reads / writes its own record with VEC-wide shared-memory accesses: VEC = 4, 2 or 1 floats,
+// the widest that divides NW, which is bank-conflict free for the benchmarked records (14 -> LDS.64, 20 -> LDS.128,
+// 17 -> LDS.32 at an odd stride).
+template <int NW> struct TileVec { static constexpr int V = NW % 4 == 0 ? 4 : (NW % 2 == 0 ? 2 : 1); };
 
+template <int NT>
+__device__ __forceinline__ void flat_copy(float *__restrict__ dst, const float *__restrict__ src, int total) {
+    const int tid = threadIdx.x;
+    if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
+        const int nv = total >> 2;
+        const float4 *s4 = reinterpret_cast<const float4 *>(src);
+        float4 *d4 = reinterpret_cast<float4 *>(dst);
+        for (int e = tid; e < nv; e += NT) d4[e] = s4[e];
+        for (int e = (nv << 2) + tid; e < total; e += NT) dst[e] = src[e];
+    } else {
+        for (int e = tid; e < total; e += NT) dst[e] = src[e];
+    }
+}
+template <int NW>
+__device__ __forceinline__ void tile_get(const float *tile, int r, float *reg) {
+    constexpr int V = TileVec<NW>::V;
+    const float *row = tile + r * NW;
+    if constexpr (V == 4) {
+#pragma unroll
+        for (int k = 0; k < NW; k += 4) {
+            const float4 v = *reinterpret_cast<const float4 *>(row + k);
+            reg[k] = v.x; reg[k + 1] = v.y; reg[k + 2] = v.z; reg[k + 3] = v.w;
+        }
+    } else if constexpr (V == 2) {
+#pragma unroll
+        for (int k = 0; k < NW; k += 2) {
+            const float2 v = *reinterpret_cast<const float2 *>(row + k);
+            reg[k] = v.x; reg[k + 1] = v.y;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < NW; ++k) reg[k] = row[k];
+    }
+}
+template <int NW>
+__device__ __forceinline__ void tile_put(float *tile, int r, const float *reg) {
+    constexpr int V = TileVec<NW>::V;
+    float *row = tile + r * NW;
+    if constexpr (V == 4) {
+#pragma unroll
+        for (int k = 0; k < NW; k += 4) *reinterpret_cast<float4 *>(row + k) = make_float4(reg[k], reg[k + 1], reg[k + 2], reg[k + 3]);
+    } else if constexpr (V == 2) {
+#pragma unroll
+        for (int k = 0; k < NW; k += 2) *reinterpret_cast<float2 *>(row + k) = make_float2(reg[k], reg[k + 1]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < NW; ++k) row[k] = reg[k];
+    }
+}
+// whole-tile staging, HBM -> shared (any record stride)
+template <int NW, int NT>
+__device__ __forceinline__ void tile_stage_in(const float *__restrict__ w, int64_t ld, int64_t base, int64_t n, float *tile) {
+    const int cnt = (int)min((int64_t)NT, n - base);
+    if (ld == NW) {
+        flat_copy<NT>(tile, w + base * NW, cnt * NW);
+    } else if ((int)threadIdx.x < cnt) {
+        const float *src = w + (base + threadIdx.x) * ld;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) tile[threadIdx.x * NW + k] = __ldg(src + k);
+    }
+}
+template <int NW, int NT>
+__device__ __forceinline__ void tile_stage_out(float *__restrict__ w, int64_t ld, int64_t base, int64_t n, const float *tile) {
+    const int cnt = (int)min((int64_t)NT, n - base);
+    if (ld == NW) {
+        flat_copy<NT>(w + base * NW, tile, cnt * NW);
+    } else if ((int)threadIdx.x < cnt) {
+        float *dst = w + (base + threadIdx.x) * ld;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) dst[k] = tile[threadIdx.x * NW + k];
+    }
+}
+// tile + registers in one go (the register-resident kernels)
 template <int NW>
 __device__ __forceinline__ void tile_load(const float *__restrict__ w, int64_t ld, int64_t base, int64_t n,
                                           float *tile, float *reg) {
-    const int tid = threadIdx.x;
-    const int cnt = (int)min((int64_t)BS, n - base);
-    if (ld == NW) {
-        const float *src = w + base * NW;
-        for (int e = tid; e < cnt * NW; e += BS) tile[(e / NW) * tile_stride<NW>() + (e % NW)] = __ldg(src + e);
-        __syncthreads();
-        if (tid < cnt) {
-#pragma unroll
-            for (int k = 0; k < NW; ++k) reg[k] = tile[tid * tile_stride<NW>() + k];
-        }
-    } else if (tid < cnt) {
-        const float *src = w + (base + tid) * ld;
-#pragma unroll
-        for (int k = 0; k < NW; ++k) reg[k] = __ldg(src + k);
-    }
+    tile_stage_in<NW, BS>(w, ld, base, n, tile);
+    __syncthreads();
+    if (base + threadIdx.x < n) tile_get<NW>(tile, threadIdx.x, reg);
 }
 template <int NW>
 __device__ __forceinline__ void tile_store(float *__restrict__ w, int64_t ld, int64_t base, int64_t n, float *tile,
                                            const float *reg) {
-    const int tid = threadIdx.x;
-    const int cnt = (int)min((int64_t)BS, n - base);
-    if (ld == NW) {
-        __syncthreads();  // tile may still be read by slower threads of a previous phase
-        if (tid < cnt) {
-#pragma unroll
-            for (int k = 0; k < NW; ++k) tile[tid * tile_stride<NW>() + k] = reg[k];
-        }
-        __syncthreads();
-        float *dst = w + base * NW;
-        for (int e = tid; e < cnt * NW; e += BS) dst[e] = tile[(e / NW) * tile_stride<NW>() + (e % NW)];
-    } else if (tid < cnt) {
-        float *dst = w + (base + tid) * ld;
-#pragma unroll
-        for (int k = 0; k < NW; ++k) dst[k] = reg[k];
-    }
+    __syncthreads();  // tile may still be read by slower threads of a previous phase
+    if (base + threadIdx.x < n) tile_put<NW>(tile, threadIdx.x, reg);
+    __syncthreads();
+    tile_stage_out<NW, BS>(w, ld, base, n, tile);
 }
 template <int NW>
 __device__ __forceinline__ void record_load(const float *__restrict__ w, int64_t ld, int64_t i, float *reg) {
@@ -122,7 +186,7 @@ __device__ __forceinline__ void block_histogram(int cls, bool active, unsigned i
 template <class S>
 __global__ void __launch_bounds__(BS) self_apply_fixed_kernel(float *__restrict__ w, int64_t ld, int64_t n,
                                                               int n_steps) {
-    __shared__ float tile[BS * tile_stride<S::NW>()];
+    __shared__ __align__(16) float tile[BS * S::NW];
     const int64_t base = (int64_t)blockIdx.x * BS;
     float a[S::NW], b[S::NW];
     tile_load<S::NW>(w, ld, base, n, tile, a);
@@ -149,7 +213,7 @@ __global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restric
                                                                 uint8_t *__restrict__ cls_out,
                                                                 unsigned long long *counters,
                                                                 float *__restrict__ traj) {
-    __shared__ float tile[BS * tile_stride<S::NW>()];
+    __shared__ __align__(16) float tile[BS * S::NW];
     __shared__ unsigned int hist[5];
     const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
     const bool active = i < n;
@@ -227,7 +291,7 @@ template <class S>
 __global__ void __launch_bounds__(BS) classify_kernel(const float *__restrict__ w, int64_t ld, int64_t n, Eps eps,
                                                       int with_fix_sec, uint8_t *__restrict__ cls_out,
                                                       uint8_t *__restrict__ flags_out, unsigned long long *counters) {
-    __shared__ float tile[BS * tile_stride<S::NW>()];
+    __shared__ __align__(16) float tile[BS * S::NW];
     __shared__ unsigned int hist[5];
     const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
     const bool active = i < n;
@@ -287,7 +351,7 @@ __global__ void __launch_bounds__(BS) train_kernel(float *__restrict__ w, int64_
                                                    const int32_t *__restrict__ teacher_idx,
                                                    double *__restrict__ loss_out) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ float tile[BS * tile_stride<S::NW>()];
+    __shared__ __align__(16) float tile[BS * S::NW];
     const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
     const bool active = i < n;
     SgdScratch sc = sgd_scratch<S>(smem, BS);
@@ -372,6 +436,7 @@ struct SoupP {
     int train, severity, remove_divergent, remove_zero, perm_mode;
     float lr;
     Eps eps;
+    int path;  // 0 auto, 1 fused single kernel, 2 multi-pass
 };
 
 __device__ __forceinline__ void soup_draw(const SoupP &p, uint64_t seed, uint64_t slot, uint64_t gen,
@@ -486,53 +551,320 @@ __global__ void __launch_bounds__(BS) soup_lists_kernel(SoupP p, uint64_t seed, 
     if (at >= slot0 && at < slot0 + n) next[a] = atomicExch(&head[at - slot0], (int32_t)a);
 }
 
-// phase B: the victim's owner thread applies its attackers in ascending index, then learn_from / train / cull.
+// Where the start-of-generation records live: shard r holds global particles [r*len, (r+1)*len).  One shard =
+// a plain (gathered or unsharded) arena; several = the ranks' own arenas mapped into this process (NVLink peer
+// memory), so partner records are fetched straight from their owner GPU and no all-gather is needed.
+struct ShardTable {
+    const float *base[SRNN_MAX_SHARDS];
+    int64_t len;
+    int32_t n;
+};
+__device__ __forceinline__ const float *shard_record(const ShardTable &t, int64_t ld, int64_t g) {
+    const uint32_t r = t.n == 1 ? 0u : (uint32_t)g / (uint32_t)t.len;  // n_total < 2^31
+    return t.base[r] + (g - (int64_t)r * t.len) * ld;
+}
+
 template <class S>
-__global__ void __launch_bounds__(BS) soup_sync_kernel(const float *__restrict__ snap, int64_t snap_ld,
+__device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t snap_ld, const int32_t *__restrict__ head,
+                                             const int32_t *__restrict__ next, int64_t v, float *cur);
+
+// phase B.  The CTA keeps its 256 records in shared memory and runs the generation as a sequence of phases; the
+// rare events of each phase (a particle that is attacked: ~10 %, one that learns: ~10 %, one that dies) are
+// COMPACTED into a queue and handed to the first threads of the CTA, so whole warps skip a phase instead of every
+// warp executing every path for one or two of its lanes.  Results do not depend on who processes a particle.
+#ifndef SRNN_SOUP_MINB
+#define SRNN_SOUP_MINB 10
+#endif
+template <class S, int SBS>
+__global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_sync_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
                                                        int64_t n_total, float *__restrict__ w_out, int64_t out_ld,
                                                        int64_t slot0, int64_t n, SoupP p, uint64_t seed, uint64_t gen,
                                                        Limits lim, const int32_t *__restrict__ head,
                                                        const int32_t *__restrict__ next, uint8_t *action,
                                                        double *loss, uint8_t *dead_out) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ float tile[BS * tile_stride<S::NW>()];
-    const int64_t base = (int64_t)blockIdx.x * BS, i = base + threadIdx.x;
+    constexpr int NW = S::NW;
+    __shared__ __align__(16) float tile[SBS * NW];
+    __shared__ int32_t lrn_s[SBS];
+    __shared__ uint16_t queue[SBS];
+    __shared__ int q_len;
+    const int tid = threadIdx.x;
+    const int64_t base = (int64_t)blockIdx.x * SBS, i = base + tid;
     const bool active = i < n;
-    SgdScratch sc = sgd_scratch<S>(smem, BS);
-    float cur[S::NW];
-    tile_load<S::NW>(snap + slot0 * snap_ld, snap_ld, base, n, tile, cur);
+    SgdScratch sc = sgd_scratch<S>(smem, SBS);
+    // ---- stage the CTA's own records (flat vector copy when packed)
+    tile_stage_in<NW, SBS>(own, snap_ld, base, n, tile);
+    if (tid == 0) q_len = 0;
+    int64_t at = -1, lr = -1;
+    if (active) soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at, &lr);
     __syncthreads();
+    // ---- phase 1: particles hit by attackers (code/soup.py:56-61 seen from the victim)
+    if (active && head[i] >= 0) queue[atomicAdd(&q_len, 1)] = (uint16_t)tid;
+    __syncthreads();
+    if (tid < q_len) {
+        const int v = queue[tid];
+        float cur[NW];
+        tile_get<NW>(tile, v, cur);
+        attack_chain<S>(snap, snap_ld, head, next, base + v, cur);
+        tile_put<NW>(tile, v, cur);
+    }
+    __syncthreads();
+    // ---- phase 2: learn_from x severity (code/soup.py:62-68), teacher read from the snapshot
+    const int sev = p.severity > 0 ? p.severity : 0, tr = p.train > 0 ? p.train : 0;
+    const uint64_t ep = gen * (uint64_t)(sev + tr);
+    const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
+    if (tid == 0) q_len = 0;
+    lrn_s[tid] = (int32_t)lr;
+    __syncthreads();
+    if (active && lr >= 0 && sev > 0) queue[atomicAdd(&q_len, 1)] = (uint16_t)tid;
+    __syncthreads();
+    if (tid < q_len) {
+        const int v = queue[tid];
+        float cur[NW];
+        tile_get<NW>(tile, v, cur);
+        const float *rec = shard_record(snap, snap_ld, lrn_s[v]);
+#pragma unroll
+        for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = __ldg(rec + k);
+        for (int e = 0; e < sev; ++e) {
+            if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + base + v), ep + (uint64_t)e, sc.ord, sc.stride);
+            train_epoch<S>(cur, sc, ordered, p.lr);
+        }
+        tile_put<NW>(tile, v, cur);
+    }
+    __syncthreads();
+    // ---- phase 3: self-training (every particle, code/soup.py:69-76) and the cull tests (:77-86)
+    float cur[NW];
+    tile_get<NW>(tile, tid, cur);
+    double ls = nan("");
+    int dead = 0;
+    if (active) {
+        for (int e = 0; e < tr; ++e) {
+#pragma unroll
+            for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+            if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + i), ep + (uint64_t)(sev + e), sc.ord, sc.stride);
+            ls = train_epoch<S>(cur, sc, ordered, p.lr);
+        }
+        if (tr > 0) tile_put<NW>(tile, tid, cur);
+        if (p.remove_divergent && is_diverged<NW>(cur)) dead = SRNN_ACT_DIV_DEAD;
+        if (p.remove_zero && is_zero<NW>(cur, p.eps.le)) dead = SRNN_ACT_ZERO_DEAD;
+    }
+    if (tid == 0) q_len = 0;
+    __syncthreads();
+    // ---- phase 4: respawn (generate_particle): a pure function of (seed, slot, generation)
+    if (dead) queue[atomicAdd(&q_len, 1)] = (uint16_t)tid;
+    __syncthreads();
+    if (tid < q_len) {
+        const int v = queue[tid];
+        float fresh[NW];
+        init_net<S>(seed, (uint64_t)(slot0 + base + v), (uint32_t)gen, lim, fresh);
+        tile_put<NW>(tile, v, fresh);
+    }
     if (active) {
         uint8_t act = SRNN_ACT_NONE;
-        double ls = nan("");
-        bool dead = false;
-        int64_t at, lr;
-        soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at, &lr);
         if (at >= 0) act = SRNN_ACT_ATTACK;
-        int32_t last = -1;
-        for (;;) {  // lists are short (Poisson(attacking_rate)): select the next-larger attacker by rescanning
-            int32_t best = 0x7fffffff;
-            for (int32_t a = head[i]; a >= 0; a = next[a])
-                if (a > last && a < best) best = a;
-            if (best == 0x7fffffff) break;
-            float op[S::NW], res[S::NW];
-            record_load<S::NW>(snap, snap_ld, best, op);
-            net_apply<S>(op, cur, res);
-#pragma unroll
-            for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
-            last = best;
-        }
-        if (lr >= 0) {
-            const float *tr = snap + lr * snap_ld;
-#pragma unroll
-            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = __ldg(tr + k);
-        }
-        soup_tail<S>(p, cur, sc, lr >= 0, false, seed, (uint64_t)(slot0 + i), gen, lim, &act, &ls, nullptr, 0, 0, &dead);
+        if (lr >= 0) act = SRNN_ACT_LEARN;
+        if (tr > 0) act = SRNN_ACT_TRAIN;
+        if (dead) act = (uint8_t)dead;
         if (action) action[i] = act;
         if (loss) loss[i] = ls;
         if (dead_out) dead_out[i] = dead ? 1 : 0;
     }
-    tile_store<S::NW>(w_out, out_ld, base, n, tile, cur);
+    __syncthreads();
+    // ---- write the new generation
+    tile_stage_out<NW, SBS>(w_out, out_ld, base, n, tile);
+}
+
+// ---------------------------------------------------------------------------------------------- multi-pass path
+// For large soups the generation is split into dense passes over GLOBALLY compacted work lists, so that every warp
+// of every pass is full and the long-latency chains (list walk -> partner gather -> operator / SGD) of a million
+// particles overlap each other instead of serialising inside a CTA:
+//   events   : every global particle draws its pairing; local victims / learners are appended to work lists
+//   victims  : one thread per attacked particle: apply its attackers (ascending index) -> w_out
+//   learners : one thread per learning particle: learn_from x severity -> w_out
+//   final    : streaming pass over all local particles: pick up touched records, train, cull, respawn -> w_out
+// scratch layout (int32 words): head[n] | next[n_total] | victims[n] | learners[n] | flags (n bytes) | counters[4]
+enum { FLAG_ATTACKS = 1, FLAG_LEARNS = 2 };
+
+__device__ __forceinline__ void warp_push(int32_t *counter, int32_t *list, int32_t value, bool pred) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (!m) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    int32_t start = 0;
+    if (lane == leader) start = atomicAdd(counter, __popc(m));
+    start = __shfl_sync(0xffffffffu, start, leader);
+    if (pred) list[start + __popc(m & ((1u << lane) - 1u))] = value;
+}
+
+constexpr int EV_BS = 1024;
+// One global atomic per CTA and list: the CTA counts its pushes in shared memory, reserves a range, then writes.
+__global__ void __launch_bounds__(EV_BS) soup_events_kernel(SoupP p, uint64_t seed, uint64_t gen, int64_t n_total,
+                                                            int64_t slot0, int64_t n, int32_t *head, int32_t *next,
+                                                            int32_t *victims, int32_t *learners, uint8_t *flags,
+                                                            int32_t *counters) {
+    __shared__ int cnt_s[2], base_s[2];
+    if (threadIdx.x < 2) cnt_s[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t a = (int64_t)blockIdx.x * EV_BS + threadIdx.x;
+    int64_t at = -1, lr = -1;
+    if (a < n_total) soup_draw(p, seed, (uint64_t)a, gen, n_total, &at, &lr);
+    bool first_hit = false;
+    if (at >= slot0 && at < slot0 + n) {
+        const int32_t prev = atomicExch(&head[at - slot0], (int32_t)a);
+        next[a] = prev;
+        first_hit = prev < 0;
+    }
+    const bool local = a >= slot0 && a < slot0 + n;
+    const bool learns = local && lr >= 0 && p.severity > 0;
+    if (local) flags[a - slot0] = (uint8_t)((at >= 0 ? FLAG_ATTACKS : 0) | (lr >= 0 ? FLAG_LEARNS : 0));
+    const int my_v = first_hit ? atomicAdd(&cnt_s[0], 1) : -1;
+    const int my_l = learns ? atomicAdd(&cnt_s[1], 1) : -1;
+    __syncthreads();
+    if (threadIdx.x < 2 && cnt_s[threadIdx.x]) base_s[threadIdx.x] = atomicAdd(&counters[threadIdx.x], cnt_s[threadIdx.x]);
+    __syncthreads();
+    if (first_hit) victims[base_s[0] + my_v] = (int32_t)(at - slot0);
+    if (learns) learners[base_s[1] + my_l] = (int32_t)(a - slot0);
+}
+
+// apply the attackers of local particle v (list head[v] -> next[...]) to `cur` in ascending attacker index
+template <class S>
+__device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t snap_ld, const int32_t *__restrict__ head,
+                                             const int32_t *__restrict__ next, int64_t v, float *cur) {
+    int32_t last = -1;
+    for (;;) {  // lists are short (Poisson(attacking_rate)): select the next-larger attacker by rescanning
+        int32_t best = 0x7fffffff, larger = 0;
+        for (int32_t a = head[v]; a >= 0; a = next[a])
+            if (a > last) { ++larger; if (a < best) best = a; }
+        if (larger == 0) break;
+        float op[S::NW], res[S::NW];
+        const float *rec = shard_record(snap, snap_ld, best);
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) op[k] = __ldg(rec + k);
+        net_apply<S>(op, cur, res);
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
+        if (larger == 1) break;  // that was the last one: no need to walk the list again
+        last = best;
+    }
+}
+
+template <class S>
+__global__ void __launch_bounds__(BS) soup_victims_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
+                                                          float *__restrict__ w_out, int64_t out_ld,
+                                                          const int32_t *__restrict__ head,
+                                                          const int32_t *__restrict__ next,
+                                                          const int32_t *__restrict__ victims,
+                                                          const int32_t *__restrict__ counters) {
+    const int64_t t = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (t >= counters[0]) return;
+    const int64_t v = victims[t];
+    float cur[S::NW];
+    record_load<S::NW>(own, snap_ld, v, cur);
+    attack_chain<S>(snap, snap_ld, head, next, v, cur);
+    record_store<S::NW>(w_out, out_ld, v, cur);
+}
+
+template <class S>
+__global__ void __launch_bounds__(BS) soup_learners_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
+                                                           int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0,
+                                                           SoupP p, uint64_t seed, uint64_t gen,
+                                                           const int32_t *__restrict__ head,
+                                                           const int32_t *__restrict__ learners,
+                                                           const int32_t *__restrict__ counters) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    SgdScratch sc = sgd_scratch<S>(smem, BS);
+    __syncthreads();  // position codes visible
+    const int64_t t = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (t >= counters[1]) return;
+    const int64_t l = learners[t];
+    float cur[S::NW];
+    if (head[l] >= 0) {  // attacked earlier in this generation: continue from the victims pass' result
+        const float *rec = w_out + l * out_ld;
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) cur[k] = rec[k];
+    } else {
+        record_load<S::NW>(own, snap_ld, l, cur);
+    }
+    int64_t at, lr;
+    soup_draw(p, seed, (uint64_t)(slot0 + l), gen, n_total, &at, &lr);
+    const float *rec = shard_record(snap, snap_ld, lr);
+#pragma unroll
+    for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = __ldg(rec + k);
+    const int sev = p.severity > 0 ? p.severity : 0, tr = p.train > 0 ? p.train : 0;
+    const uint64_t ep = gen * (uint64_t)(sev + tr);
+    const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
+    for (int e = 0; e < sev; ++e) {
+        if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + l), ep + (uint64_t)e, sc.ord, sc.stride);
+        train_epoch<S>(cur, sc, ordered, p.lr);
+    }
+    record_store<S::NW>(w_out, out_ld, l, cur);
+}
+
+template <class S>
+__global__ void __launch_bounds__(BS) soup_final_kernel(const float *__restrict__ own, int64_t snap_ld, float *w_out,
+                                                        int64_t out_ld, int64_t slot0, int64_t n, SoupP p, uint64_t seed,
+                                                        uint64_t gen, Limits lim, const int32_t *__restrict__ head,
+                                                        const uint8_t *__restrict__ flags, uint8_t *action, double *loss,
+                                                        uint8_t *dead_out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int NW = S::NW;
+    __shared__ __align__(16) float tile[BS * NW];
+    __shared__ uint16_t queue[BS];
+    __shared__ int q_len;
+    const int tid = threadIdx.x;
+    const int64_t base = (int64_t)blockIdx.x * BS, i = base + tid;
+    const bool active = i < n;
+    const int tr = p.train > 0 ? p.train : 0, sev = p.severity > 0 ? p.severity : 0;
+    SgdScratch sc;
+    if (tr > 0) sc = sgd_scratch<S>(smem, BS);
+    tile_stage_in<NW, BS>(own, snap_ld, base, n, tile);
+    if (tid == 0) q_len = 0;
+    __syncthreads();
+    float cur[NW];
+    uint8_t fl = 0;
+    double ls = nan("");
+    int dead = 0;
+    if (active) {
+        fl = flags[i];
+        const bool touched = head[i] >= 0 || ((fl & FLAG_LEARNS) && sev > 0);
+        if (touched) {  // the victims / learners passes left this particle's record in w_out
+            const float *rec = w_out + i * out_ld;
+#pragma unroll
+            for (int k = 0; k < NW; ++k) cur[k] = rec[k];
+        } else {
+            tile_get<NW>(tile, tid, cur);
+        }
+        const uint64_t ep = gen * (uint64_t)(sev + tr);
+        const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
+        for (int e = 0; e < tr; ++e) {
+#pragma unroll
+            for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+            if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + i), ep + (uint64_t)(sev + e), sc.ord, sc.stride);
+            ls = train_epoch<S>(cur, sc, ordered, p.lr);
+        }
+        if (touched || tr > 0) tile_put<NW>(tile, tid, cur);
+        if (p.remove_divergent && is_diverged<NW>(cur)) dead = SRNN_ACT_DIV_DEAD;
+        if (p.remove_zero && is_zero<NW>(cur, p.eps.le)) dead = SRNN_ACT_ZERO_DEAD;
+    }
+    if (dead) queue[atomicAdd(&q_len, 1)] = (uint16_t)tid;
+    __syncthreads();
+    if (tid < q_len) {  // respawn, compacted within the CTA
+        const int v = queue[tid];
+        float fresh[NW];
+        init_net<S>(seed, (uint64_t)(slot0 + base + v), (uint32_t)gen, lim, fresh);
+        tile_put<NW>(tile, v, fresh);
+    }
+    if (active) {
+        uint8_t act = SRNN_ACT_NONE;
+        if (fl & FLAG_ATTACKS) act = SRNN_ACT_ATTACK;
+        if (fl & FLAG_LEARNS) act = SRNN_ACT_LEARN;
+        if (tr > 0) act = SRNN_ACT_TRAIN;
+        if (dead) act = (uint8_t)dead;
+        if (action) action[i] = act;
+        if (loss) loss[i] = ls;
+        if (dead_out) dead_out[i] = dead ? 1 : 0;
+    }
+    __syncthreads();
+    tile_stage_out<NW, BS>(w_out, out_ld, base, n, tile);
 }
 
 // ================================================================================================ uid scan
@@ -619,6 +951,7 @@ static int make_soup(const srnn_soup_params *p, SoupP *q) {
     q->remove_zero = p->remove_zero;
     q->perm_mode = p->perm_mode;
     q->lr = p->lr;
+    q->path = p->engine_path;
     if (p->perm_mode != SRNN_PERM_NONE && p->perm_mode != SRNN_PERM_PHILOX)
         return fail(SRNN_ERR_ARG, "soup perm_mode must be SRNN_PERM_NONE or SRNN_PERM_PHILOX%s");
     return make_eps(p->epsilon, &q->eps);
@@ -784,7 +1117,7 @@ int srnn_train(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t 
     SRNN_CHECK_ARENA(w, ld, S)                                                                               \
     if (teacher_w && teacher_ld < S::NW) return fail(SRNN_ERR_ARG, "teacher_ld is smaller than n_weights%s"); \
     const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
-    int rc = allow_smem(train_kernel<S>, sm + sizeof(float) * BS * tile_stride<S::NW>());                    \
+    int rc = allow_smem(train_kernel<S>, sm + sizeof(float) * BS * S::NW);                    \
     if (rc) return rc;                                                                                       \
     train_kernel<S><<<grid_for(n), BS, sm, (cudaStream_t)stream>>>(w, ld, n, n_epochs, lr, perm_mode, perm, seed, slot0, \
                                                                    epoch0, teacher_w, teacher_ld, teacher_idx, loss_out);
@@ -848,33 +1181,92 @@ int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *
     return check_launch("srnn_soup_ordered");
 }
 
-int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const float *snap, int64_t snap_ld,
-                   int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed, uint64_t gen,
-                   int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream) {
+static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, const ShardTable &tab, const float *own,
+                          int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n,
+                          uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead,
+                          void *stream) {
     if (!d || !scratch) return fail(SRNN_ERR_ARG, "desc or scratch is NULL%s");
     if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
     if (n_total >= 0x7fffffffLL || slot0 < 0 || slot0 + n > n_total)
         return fail(SRNN_ERR_ARG, "need 0 <= slot0, slot0 + n <= n_total < 2^31%s");
-    if ((const float *)w_out == snap) return fail(SRNN_ERR_ARG, "w_out must not alias snap%s");
     SoupP q;
     int rc = make_soup(p, &q);
     if (rc) return rc;
     const Limits lim = make_limits(d);
     int32_t *head = scratch, *next = scratch + n;
-    cudaError_t ce = cudaMemsetAsync(head, 0xFF, sizeof(int32_t) * (size_t)n, (cudaStream_t)stream);
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t ce = cudaMemsetAsync(head, 0xFF, sizeof(int32_t) * (size_t)n, st);
     if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    const bool multipass = q.path == 2 || (q.path == 0 && n >= SOUP_MULTIPASS_MIN);
+    if (multipass) {
+        int32_t *victims = next + n_total, *learners = victims + n;
+        uint8_t *flags = reinterpret_cast<uint8_t *>(learners + n);
+        int32_t *counters = learners + n + (n + 3) / 4;
+        ce = cudaMemsetAsync(counters, 0, sizeof(int32_t) * 4, st);
+        if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+        soup_events_kernel<<<(unsigned)((n_total + EV_BS - 1) / EV_BS), EV_BS, 0, st>>>(q, seed, gen, n_total, slot0, n, head,
+                                                                                        next, victims, learners, flags, counters);
+#define BODY(S)                                                                                              \
+    if (snap_ld < S::NW || out_ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s"); \
+    const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
+    rc = allow_smem(soup_learners_kernel<S>, sm);                                                            \
+    if (!rc) rc = allow_smem(soup_final_kernel<S>, sm + sizeof(float) * BS * S::NW + 1024);                  \
+    if (rc) return rc;                                                                                       \
+    if (q.attacking_rate > 0.0)                                                                              \
+        soup_victims_kernel<S><<<grid_for(n), BS, 0, st>>>(tab, own, snap_ld, w_out, out_ld, head, next, victims, counters); \
+    if (q.learn_from_rate > 0.0 && q.severity > 0)                                                           \
+        soup_learners_kernel<S><<<grid_for(n), BS, sm, st>>>(tab, own, snap_ld, n_total, w_out, out_ld, slot0, q, seed, gen, \
+                                                             head, learners, counters);                      \
+    soup_final_kernel<S><<<grid_for(n), BS, q.train > 0 ? sm : 0, st>>>(own, snap_ld, w_out, out_ld, slot0, n, q, seed, gen, \
+                                                                       lim, head, flags, action, loss, dead);
+        SRNN_DISPATCH(d)
+#undef BODY
+        return check_launch("srnn_soup_sync (multi-pass)");
+    }
     if (q.attacking_rate > 0.0)
         soup_lists_kernel<<<grid_for(n_total), BS, 0, (cudaStream_t)stream>>>(q, seed, gen, n_total, slot0, n, head, next);
 #define BODY(S)                                                                                              \
-    SRNN_CHECK_ARENA(snap, snap_ld, S) SRNN_CHECK_ARENA(w_out, out_ld, S)                                    \
-    const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
-    rc = allow_smem(soup_sync_kernel<S>, sm + sizeof(float) * BS * tile_stride<S::NW>());                    \
-    if (rc) return rc;                                                                                       \
-    soup_sync_kernel<S><<<grid_for(n), BS, sm, (cudaStream_t)stream>>>(snap, snap_ld, n_total, w_out, out_ld, slot0, n, q, \
-                                                                       seed, gen, lim, head, next, action, loss, dead);
+    if (snap_ld < S::NW || out_ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s"); \
+    constexpr int SBS = SOUP_BS;                                                                             \
+    const size_t sm = sgd_smem_bytes<S>(SBS);                                                                \
+    soup_sync_kernel<S, SBS><<<(unsigned)((n + SBS - 1) / SBS), SBS, sm, (cudaStream_t)stream>>>(            \
+        tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead);
     SRNN_DISPATCH(d)
 #undef BODY
     return check_launch("srnn_soup_sync");
+}
+
+int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const float *snap, int64_t snap_ld,
+                   int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed, uint64_t gen,
+                   int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream) {
+    if (!snap || !w_out) return fail(SRNN_ERR_ARG, "arena pointer is NULL%s");
+    if ((const float *)w_out == snap) return fail(SRNN_ERR_ARG, "w_out must not alias snap%s");
+    ShardTable tab;
+    memset(&tab, 0, sizeof tab);
+    tab.base[0] = snap;
+    tab.len = n_total;
+    tab.n = 1;
+    return soup_sync_impl(d, p, tab, snap + slot0 * snap_ld, snap_ld, n_total, w_out, out_ld, slot0, n, seed, gen, scratch,
+                          action, loss, dead, stream);
+}
+
+int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, const float *const *shards, int32_t n_shards,
+                         int64_t shard_len, int32_t my_shard, int64_t ld, float *w_out, int64_t out_ld, uint64_t seed,
+                         uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream) {
+    if (!shards || !w_out) return fail(SRNN_ERR_ARG, "shards or w_out is NULL%s");
+    if (n_shards < 1 || n_shards > SRNN_MAX_SHARDS || my_shard < 0 || my_shard >= n_shards)
+        return fail(SRNN_ERR_ARG, "need 1 <= n_shards <= SRNN_MAX_SHARDS and 0 <= my_shard < n_shards%s");
+    ShardTable tab;
+    memset(&tab, 0, sizeof tab);
+    for (int r = 0; r < n_shards; ++r) {
+        if (!shards[r]) return fail(SRNN_ERR_ARG, "a shard pointer is NULL%s");
+        if (shards[r] == w_out) return fail(SRNN_ERR_ARG, "w_out must not alias a shard%s");
+        tab.base[r] = shards[r];
+    }
+    tab.len = shard_len;
+    tab.n = n_shards;
+    return soup_sync_impl(d, p, tab, shards[my_shard], ld, shard_len * n_shards, w_out, out_ld, (int64_t)my_shard * shard_len,
+                          shard_len, seed, gen, scratch, action, loss, dead, stream);
 }
 
 int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w_a, float *w_b, int64_t ld, int64_t n,

@@ -277,14 +277,15 @@ class PopulationSoup:
         self.slot0, self.n_local = shard_of(self.size, self.world, self.rank)
         self.seed, self.time = int(seed), 0
         self.params = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1,
-                           remove_divergent=False, remove_zero=False, epsilon=1e-4, perm_mode=_eng.PERM_PHILOX)
+                           remove_divergent=False, remove_zero=False, epsilon=1e-4, perm_mode=_eng.PERM_PHILOX,
+                           engine_path=0)
         self.params.update(params)
         self.backend = backend or _CudaBackend(device)
         nw, B = self.desc.n_weights, self.backend
         self.w = B.alloc((self.n_local, nw), torch.float32)
         self._next = B.alloc((self.n_local, nw), torch.float32)
         self._snap = B.alloc((self.size, nw), torch.float32) if self.world > 1 else None
-        self._scratch = B.alloc((self.size + self.n_local,), torch.int32)
+        self._scratch = B.alloc((_eng.soup_scratch_len(self.size, self.n_local),), torch.int32)
         self.dead = B.alloc((self.n_local,), torch.uint8)
         self.action = B.alloc((self.n_local,), torch.uint8)
         self.uid = B.alloc((self.n_local,), torch.int64)
@@ -310,7 +311,7 @@ class PopulationSoup:
 
     def _sp(self):
         return {k: self.params[k] for k in ("attacking_rate", "learn_from_rate", "train", "learn_from_severity",
-                                            "remove_divergent", "remove_zero", "epsilon", "perm_mode")}
+                                            "remove_divergent", "remove_zero", "epsilon", "perm_mode", "engine_path")}
 
     def evolve(self, iterations=1):
         import torch.distributed as dist

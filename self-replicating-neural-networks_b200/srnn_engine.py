@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsrnn_b200.so")
+LIB_PATH = os.environ.get("SRNN_LIB", os.path.join(_HERE, "libsrnn_b200.so"))   # SRNN_LIB: A/B-test another build
 
 KIND_WW, KIND_AGG, KIND_RNN = 0, 1, 2
 KIND_NAMES = {KIND_WW: "WeightwiseNeuralNetwork", KIND_AGG: "AggregatingNeuralNetwork", KIND_RNN: "RecurrentNeuralNetwork"}
@@ -28,7 +28,7 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_sync", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
 UIDS_STATIC_MAX = 1 << 24
 
 
@@ -43,7 +43,8 @@ class NetDesc(C.Structure):
 class SoupParams(C.Structure):
     _fields_ = [("attacking_rate", C.c_double), ("learn_from_rate", C.c_double), ("train", C.c_int32),
                 ("learn_from_severity", C.c_int32), ("remove_divergent", C.c_int32), ("remove_zero", C.c_int32),
-                ("epsilon", C.c_double), ("lr", C.c_float), ("perm_mode", C.c_int32)]
+                ("epsilon", C.c_double), ("lr", C.c_float), ("perm_mode", C.c_int32),
+                ("engine_path", C.c_int32)]
 
 
 class SrnnError(RuntimeError):
@@ -95,9 +96,15 @@ def layer_shapes(d):
 
 
 def make_soup_params(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, remove_divergent=False,
-                     remove_zero=False, epsilon=1e-14, lr=0.01, perm_mode=PERM_NONE):
+                     remove_zero=False, epsilon=1e-14, lr=0.01, perm_mode=PERM_NONE, engine_path=0):
     return SoupParams(float(attacking_rate), float(learn_from_rate), int(train), int(learn_from_severity),
-                      int(bool(remove_divergent)), int(bool(remove_zero)), float(epsilon), float(lr), int(perm_mode))
+                      int(bool(remove_divergent)), int(bool(remove_zero)), float(epsilon), float(lr), int(perm_mode),
+                      int(engine_path))
+
+
+def soup_scratch_len(n_total, n):
+    """int32 words of scratch srnn_soup_sync / srnn_soup_sync_peers need (include/srnn_b200.h)."""
+    return int(n_total) + 4 * int(n) + 16
 
 
 def _torch():
@@ -276,6 +283,17 @@ def soup_sync(desc, params, snap, n_total, w_out, slot0, n, seed, gen, scratch, 
     _chk(lib().srnn_soup_sync(C.byref(desc), C.byref(params), _ptr(snap), C.c_int64(snap.shape[1]), C.c_int64(n_total),
                               _ptr(w_out), C.c_int64(w_out.shape[1]), C.c_int64(slot0), C.c_int64(n), C.c_uint64(seed),
                               C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead), _stream()))
+
+
+def soup_sync_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action=None, loss=None,
+                    dead=None):
+    """One generation of a sharded soup reading partner records straight from the peers' arenas (shard_ptrs = device
+    pointers, as ints, of every rank's start-of-generation arena mapped into this process)."""
+    arr = (C.c_void_p * len(shard_ptrs))(*[C.c_void_p(int(q)) for q in shard_ptrs])
+    _chk(lib().srnn_soup_sync_peers(C.byref(desc), C.byref(params), arr, C.c_int32(len(shard_ptrs)), C.c_int64(shard_len),
+                                    C.c_int32(my_shard), C.c_int64(ld), _ptr(w_out), C.c_int64(w_out.shape[1]),
+                                    C.c_uint64(seed), C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead),
+                                    _stream()))
 
 
 def soup_sync_run(desc, params, w_a, w_b, seed, gen0, n_gens, scratch, action=None, dead=None):

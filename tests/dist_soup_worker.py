@@ -37,6 +37,7 @@ class OracleBackend:
 
     def soup_sync(self, desc, sp, snap, n_total, w_out, slot0, n, seed, gen, scratch, action, dead):
         import oracle
+        sp = {k: v for k, v in sp.items() if k != "engine_path"}
         a, _, _ = oracle.soup_sync(self._odesc(desc), oracle.soup_params(**sp), snap.numpy(), n_total, w_out.numpy(),
                                    slot0, n, seed, gen)
         action.copy_(torch.from_numpy(a))

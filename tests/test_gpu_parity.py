@@ -288,7 +288,8 @@ def test_soup_ordered_bitwise(eng, key):
 
 @pytest.mark.parametrize("key", BENCH_SHAPES)
 @pytest.mark.parametrize("train,sev", [(0, 1), (2, 3)])
-def test_soup_sync_bitwise_and_shard_invariance(eng, key, train, sev):
+@pytest.mark.parametrize("path", [1, 2])
+def test_soup_sync_bitwise_and_shard_invariance(eng, key, train, sev, path):
     """Snapshot-synchronous generations: one owner of all particles == the oracle, and two owners of half the
     population each (the multi-GPU sharding, emulated on one device) produce the same arena."""
     import torch
@@ -296,11 +297,11 @@ def test_soup_sync_bitwise_and_shard_invariance(eng, key, train, sev):
     n = 3000
     kw = dict(attacking_rate=0.4, learn_from_rate=0.2, train=train, learn_from_severity=sev, remove_divergent=True,
               remove_zero=True, epsilon=1e-4, perm_mode=2)
-    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    pg, po = eng.make_soup_params(engine_path=path, **kw), oracle.soup_params(**kw)   # fused kernel / multi-pass
     w = glorot_population(key, n, seed=51)
     snap = torch.from_numpy(w).cuda()
     ref = w.copy()
-    scratch = torch.zeros(2 * n, dtype=torch.int32, device="cuda")
+    scratch = torch.zeros(eng.soup_scratch_len(n, n), dtype=torch.int32, device="cuda")
     for gen in range(1, 4):
         out = torch.zeros_like(snap)
         action = torch.zeros(n, dtype=torch.uint8, device="cuda")
@@ -317,6 +318,13 @@ def test_soup_sync_bitwise_and_shard_invariance(eng, key, train, sev):
         eng.soup_sync(dg, pg, snap, n, o2[:half], 0, half, 23, gen, scratch)
         eng.soup_sync(dg, pg, snap, n, o2[half:], half, n - half, 23, gen, scratch)
         assert torch.equal(o2.view(torch.int32), out.view(torch.int32))
+        # peer-memory variant: the two halves live in separate arenas and partner records are fetched by pointer
+        sh = [snap[:n // 2].clone(), snap[n // 2:].clone()]
+        o3 = torch.zeros_like(snap)
+        for r in range(2):
+            eng.soup_sync_peers(dg, pg, [t.data_ptr() for t in sh], n // 2, r, sh[0].shape[1],
+                                o3[r * (n // 2):(r + 1) * (n // 2)], 23, gen, scratch)
+        assert torch.equal(o3.view(torch.int32), out.view(torch.int32))
         # uid allocation for the respawned particles
         uid = torch.arange(n, dtype=torch.int64, device="cuda")
         tmp = torch.zeros((n + 1023) // 1024 + 1, dtype=torch.int64, device="cuda")
