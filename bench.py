@@ -198,19 +198,23 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
         # sharded by particle index over the ranks with one all-gather of the record arena per generation
         third = (10_000_000 // 3) // world * world
         kw = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, epsilon=1e-4)
-        soups = [PopulationSoup(k, third, aggregates=a, seed=5 + k, **kw).seed_particles()
-                 for k, a in ((eng.KIND_WW, 0), (eng.KIND_AGG, 4), (eng.KIND_RNN, 0))]
-        for s in soups:
-            s.evolve(2)
-        if world > 1:
+        gens, res = 20, {}
+        for exchange in ("allgather", "auto"):
+            soups = [PopulationSoup(k, third, aggregates=a, seed=5 + k, exchange=exchange, **kw).seed_particles()
+                     for k, a in ((eng.KIND_WW, 0), (eng.KIND_AGG, 4), (eng.KIND_RNN, 0))]
+            for s in soups:
+                s.evolve(2)
             dist.barrier()
-        gens = 20
-        dt = sync_max(_timed(torch, lambda: [s.evolve(1) for s in soups], reps=gens))
-        gathered = sum(s.size * s.desc.n_weights * 4 for s in soups)
-        out["soup"] = {"metric": "soup generations/sec", "value": 1.0 / dt, "unit": "generations/s",
+            res[soups[0].exchange] = sync_max(_timed(torch, lambda: [s.evolve(1) for s in soups], reps=gens))
+            gathered = sum(s.size * s.desc.n_weights * 4 for s in soups)
+            del soups
+            torch.cuda.empty_cache()
+        best = min(res, key=res.get)
+        out["soup"] = {"metric": "soup generations/sec", "value": 1.0 / res[best], "unit": "generations/s",
                        "config": dict(workload="mixed_soup_10m_sharded", particles=3 * third, kinds="WW/AGG/RNN thirds",
-                                      ranks=world, generations=gens, exchange="all-gather of record arenas per generation", **kw),
-                       "allgather_bytes_per_generation_per_gpu": gathered, "allgather_gbs_if_all_time": gathered / dt / 1e9}
+                                      ranks=world, generations=gens, exchange=best, **kw),
+                       "generations_per_s_by_exchange": {k: 1.0 / v for k, v in res.items()},
+                       "allgather_bytes_per_generation_per_gpu": gathered}
     return out
 
 

@@ -233,6 +233,29 @@ class _CudaBackend:
         _eng.soup_sync(desc, _eng.make_soup_params(**sp_kwargs), snap, n_total, w_out, slot0, n, seed, gen, scratch,
                        action=action, dead=dead)
 
+    def soup_sync_peers(self, desc, sp_kwargs, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action,
+                        dead):
+        _eng.soup_sync_peers(desc, _eng.make_soup_params(**sp_kwargs), shard_ptrs, shard_len, my_shard, ld, w_out, seed,
+                             gen, scratch, action=action, dead=dead)
+
+    def peer_arena(self, n_local, nw, group):
+        """Two ping-pong arenas in NVLink-mapped symmetric memory: returns (tensor (2, n_local, nw), handle) or None
+        when peer memory cannot be set up (then the soup falls back to the all-gather exchange)."""
+        try:
+            import torch
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm
+            buf = symm.empty((2, n_local, nw), dtype=torch.float32, device=self.device)
+            hdl = symm.rendezvous(buf, group if group is not None else dist.group.WORLD)
+            if len(hdl.buffer_ptrs) != hdl.world_size or any(int(q) == 0 for q in hdl.buffer_ptrs):
+                return None
+            buf.zero_()
+            return buf, hdl
+        except Exception as exc:   # no P2P / fabric support on this box
+            import warnings
+            warnings.warn("PopulationSoup: peer memory unavailable (%s); using the all-gather exchange" % (exc,))
+            return None
+
     def soup_sync_run(self, desc, sp_kwargs, w_a, w_b, seed, gen0, n_gens, scratch, action, dead):
         _eng.soup_sync_run(desc, _eng.make_soup_params(**sp_kwargs), w_a, w_b, seed, gen0, n_gens, scratch,
                            action=action, dead=dead)
@@ -266,7 +289,7 @@ class PopulationSoup:
     so the result does not depend on how the population is sharded."""
 
     def __init__(self, kind, size, width=2, depth=2, aggregates=0, seed=0, group=None, device=None, backend=None,
-                 **params):
+                 exchange="auto", **params):
         import torch
         import torch.distributed as dist
         self.desc = _eng.make_desc(kind, width, depth, aggregates)
@@ -282,9 +305,23 @@ class PopulationSoup:
         self.params.update(params)
         self.backend = backend or _CudaBackend(device)
         nw, B = self.desc.n_weights, self.backend
-        self.w = B.alloc((self.n_local, nw), torch.float32)
-        self._next = B.alloc((self.n_local, nw), torch.float32)
-        self._snap = B.alloc((self.size, nw), torch.float32) if self.world > 1 else None
+        # exchange of a sharded soup: "peer" = partner records are read straight from the owning GPU's arena over
+        # NVLink inside the generation kernel (srnn_soup_sync_peers); "allgather" = NCCL all-gather of the arenas,
+        # then srnn_soup_sync; "auto" = peer when symmetric memory can be set up
+        self._peer = None
+        if self.world > 1 and exchange in ("auto", "peer") and hasattr(B, "peer_arena"):
+            self._peer = B.peer_arena(self.n_local, nw, group)
+            if self._peer is None and exchange == "peer":
+                raise RuntimeError("peer-memory exchange requested but symmetric memory is unavailable")
+        self.exchange = "peer" if self._peer is not None else ("allgather" if self.world > 1 else "none")
+        if self._peer is not None:
+            buf, _ = self._peer
+            self._cur = 0
+            self.w, self._next, self._snap = buf[0], buf[1], None
+        else:
+            self.w = B.alloc((self.n_local, nw), torch.float32)
+            self._next = B.alloc((self.n_local, nw), torch.float32)
+            self._snap = B.alloc((self.size, nw), torch.float32) if self.world > 1 else None
         self._scratch = B.alloc((_eng.soup_scratch_len(self.size, self.n_local),), torch.int32)
         self.dead = B.alloc((self.n_local,), torch.uint8)
         self.action = B.alloc((self.n_local,), torch.uint8)
@@ -307,6 +344,8 @@ class PopulationSoup:
     def seed_particles(self):
         """Soup.seed: fresh Keras-style nets for every local particle."""
         self.backend.init(self.desc, self.w, self.seed, self.slot0, 0)
+        if self._peer is not None:
+            self._peer[1].barrier()          # everybody's arena is initialised before anyone reads a peer
         return self
 
     def _sp(self):
@@ -326,6 +365,18 @@ class PopulationSoup:
             return self
         for _ in range(iterations):
             self.time += 1
+            if self._peer is not None:
+                buf, hdl = self._peer
+                stride = self.n_local * self.desc.n_weights * 4
+                shards = [int(q) + self._cur * stride for q in hdl.buffer_ptrs]
+                B.soup_sync_peers(self.desc, sp, shards, self.n_local, self.rank, self.desc.n_weights, self._next,
+                                  self.seed, self.time, self._scratch, self.action, self.dead)
+                hdl.barrier()                # all ranks finished reading generation g before anyone overwrites it
+                self._cur ^= 1
+                self.w, self._next = self._next, self.w
+                if self.track_uids:
+                    self._assign_uids()
+                continue
             if self.world > 1:
                 dist.all_gather_into_tensor(self._snap, self.w, group=self.group)   # NCCL over NVLink on the box
                 snap = self._snap

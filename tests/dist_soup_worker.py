@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--kind", type=int, default=0)
     ap.add_argument("--size", type=int, default=4096)
     ap.add_argument("--gens", type=int, default=4)
+    ap.add_argument("--exchange", default="auto")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     if args.backend == "nccl":
@@ -69,7 +70,8 @@ def main():
         dist.init_process_group("gloo")
     from soup import PopulationSoup
     ps = PopulationSoup(args.kind, args.size, aggregates=4 if args.kind == 1 else 0, seed=31,
-                        backend=OracleBackend() if args.backend == "gloo" else None, attacking_rate=0.3,
+                        backend=OracleBackend() if args.backend == "gloo" else None, exchange=args.exchange,
+                        attacking_rate=0.3,
                         learn_from_rate=0.2, train=1, learn_from_severity=2, remove_divergent=True, remove_zero=True,
                         epsilon=1e-4)
     ps.track_uids = True
@@ -82,7 +84,7 @@ def main():
     dist.all_gather_into_tensor(uids, ps.uid)
     if rank == 0:
         np.savez(args.out, w=full.cpu().numpy(), uid=uids.cpu().numpy(), counts=np.array(list(counts.values())),
-                 next_uid=ps.next_uid, world=world)
+                 next_uid=ps.next_uid, world=world, exchange=ps.exchange)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -33,12 +33,13 @@ def _reference(kind, size, gens):
     return w, uid, next_uid, oracle.classify(do, w, 1e-4)[1]
 
 
-def _run(backend, world, kind, size, gens, tmp_path):
-    out = str(tmp_path / ("soup_%s_%d.npz" % (backend, kind)))
+def _run(backend, world, kind, size, gens, tmp_path, exchange="auto"):
+    out = str(tmp_path / ("soup_%s_%d_%s.npz" % (backend, kind, exchange)))
     port = 29500 + (os.getpid() + kind * 7) % 2000
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "dist_soup_worker.py"),
-           "--backend", backend, "--out", out, "--kind", str(kind), "--size", str(size), "--gens", str(gens)]
+           "--backend", backend, "--out", out, "--kind", str(kind), "--size", str(size), "--gens", str(gens),
+           "--exchange", exchange]
     env = dict(os.environ, OMP_NUM_THREADS="2")
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
@@ -71,10 +72,12 @@ def test_two_ranks_gloo_equals_one(kind, tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("kind", [0, 1, 2])
-def test_two_ranks_nccl_equals_one(kind, tmp_path):
+@pytest.mark.parametrize("exchange", ["allgather", "peer"])
+def test_two_ranks_nccl_equals_one(kind, exchange, tmp_path):
+    """all-gather exchange and the fused peer-memory exchange both equal the single-owner result bit for bit."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    got = _run("nccl", 2, kind, 8192, 3, tmp_path)
-    assert int(got["world"]) == 2
+    got = _run("nccl", 2, kind, 8192, 3, tmp_path, exchange)
+    assert int(got["world"]) == 2 and str(got["exchange"]) == exchange
     _check(got, kind, 8192, 3)
