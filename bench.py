@@ -39,7 +39,7 @@ import numpy as np  # noqa: E402
 N_NETS = 1 << 24
 N_STEPS = 100
 FLOP_PER_SELF_APP = 392.0       # 14 points x 14 MAC x 2
-FP32_INSTR_PER_SELF_APP = 224.0  # pinned operation order: 14 x (8 FFMA + 6 FMUL + 2 FADD)
+FP32_INSTR_PER_SELF_APP = 224.0  # FMA-pipe lane-ops in the pinned operation order: 14 x (8 FMA + 6 MUL + 2 ADD)
 BYTES_PER_NET = 112.0           # 56 B read + 56 B write per resident episode
 # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel at 2^24 nets
 # (profiles/r01_k1_self_apply_fixed_ncu_summary.csv): 941.3 MB + 881.2 MB per launch
@@ -346,7 +346,7 @@ def main():
                                            "(algorithmic bytes per launch = 112 B x nets)",
                          "kernel": "self_apply_fixed_kernel<WW(2,2)>", "kernel_ms": kern_ms,
                          "peak_source": "FFMA-only probe kernel measured live (MEASURED_PEAKS.json has no FP32 entry)",
-                         "issue_frac": FP32_INSTR_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / probe,
+                         "fma_pipe_frac": FP32_INSTR_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / probe,
                          "hbm_gbs": BYTES_PER_NET * n / (kern_ms * 1e-3) / 1e9},
         }
         line.update(extra)

@@ -191,13 +191,14 @@ __global__ void __launch_bounds__(BS) self_apply_fixed_kernel(float *__restrict_
     float a[S::NW], b[S::NW];
     tile_load<S::NW>(w, ld, base, n, tile, a);
     if (base + threadIdx.x < n) {
+        const float one = opaque_one();
         int s = 0;
         for (; s + 2 <= n_steps; s += 2) {  // ping-pong: no register copies between steps
-            net_apply<S>(a, a, b);
-            net_apply<S>(b, b, a);
+            net_apply<S>(a, a, b, one);
+            net_apply<S>(b, b, a, one);
         }
         if (s < n_steps) {
-            net_apply<S>(a, a, b);
+            net_apply<S>(a, a, b, one);
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) a[k] = b[k];
         }
@@ -221,14 +222,14 @@ __global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restric
     tile_load<S::NW>(w, ld, base, n, tile, cur);
     int it = 0, cls = SRNN_CLS_OTHER;
     if (active) {
-        net_apply<S>(cur, cur, nxt);  // look-ahead: is_fixpoint's application IS the next self_attack
+        net_apply<S>(cur, cur, nxt, opaque_one());  // look-ahead: is_fixpoint's application IS the next self_attack
         while (it < n_steps) {
             if (mode == SRNN_RUN_UNTIL && (is_diverged<S::NW>(cur) || is_close<S::NW>(nxt, cur, eps.ge))) break;
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
             ++it;
             if (traj) record_store<S::NW>(traj + (int64_t)(it - 1) * n * ld, ld, i, cur);
-            net_apply<S>(cur, cur, nxt);
+            net_apply<S>(cur, cur, nxt, opaque_one());
         }
         if (steps_out) steps_out[i] = it;
         if (cls_out || counters) {
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(BS) apply_kernel(const float *op_w, int64_t op
 #pragma unroll
         for (int k = 0; k < S::NW; ++k) { op[k] = so[k]; in[k] = si[k]; }
     }
-    net_apply<S>(op, in, out);
+    net_apply<S>(op, in, out, opaque_one());
     record_store<S::NW>(out_w, out_ld, out_idx ? out_idx[p] : p, out);
 }
 
@@ -299,12 +300,12 @@ __global__ void __launch_bounds__(BS) classify_kernel(const float *__restrict__ 
     tile_load<S::NW>(w, ld, base, n, tile, cur);
     int cls = SRNN_CLS_OTHER;
     if (active) {
-        net_apply<S>(cur, cur, nxt);
+        net_apply<S>(cur, cur, nxt, opaque_one());
         cls = classify_with<S>(cur, nxt, eps.ge, eps.le, with_fix_sec);
         if (cls_out) cls_out[i] = (uint8_t)cls;
         if (flags_out) {
             float nn[S::NW];
-            net_apply<S>(cur, nxt, nn);
+            net_apply<S>(cur, nxt, nn, opaque_one());
             flags_out[i] = (uint8_t)((is_diverged<S::NW>(cur) ? 1 : 0) | (is_zero<S::NW>(cur, eps.le) ? 2 : 0) |
                                      (is_close<S::NW>(nxt, cur, eps.ge) ? 4 : 0) |
                                      (is_close<S::NW>(nn, cur, eps.ge) ? 8 : 0));
@@ -407,12 +408,12 @@ __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, dou
     // trial loop :69-82; after each self_attack the fixpoint test's application is the next step's result
     int tts = 0, taf = 0;
     bool still = true;
-    net_apply<S>(cur, cur, nxt);
+    net_apply<S>(cur, cur, nxt, opaque_one());
     for (int st = 0; st < max_steps; ++st) {
 #pragma unroll
         for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
         if (is_zero<S::NW>(cur, eps.le) || is_diverged<S::NW>(cur)) break;
-        net_apply<S>(cur, cur, nxt);
+        net_apply<S>(cur, cur, nxt, opaque_one());
         if (is_close<S::NW>(nxt, cur, eps.ge)) {
             if (still) ++taf;
             else still = true;
@@ -517,7 +518,7 @@ __global__ void soup_ordered_kernel(float *w, int64_t ld, int64_t n, const int64
             const float *vr = w + a * ld;
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) oth[k] = vr[k];
-            net_apply<S>(cur, oth, res);
+            net_apply<S>(cur, oth, res, opaque_one());
             record_store<S::NW>(w, ld, a, res);
             if (a == i) {
 #pragma unroll
@@ -739,7 +740,7 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
         const float *rec = shard_record(snap, snap_ld, best);
 #pragma unroll
         for (int k = 0; k < S::NW; ++k) op[k] = __ldg(rec + k);
-        net_apply<S>(op, cur, res);
+        net_apply<S>(op, cur, res, opaque_one());
 #pragma unroll
         for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
         if (larger == 1) break;  // that was the last one: no need to walk the list again
@@ -920,8 +921,22 @@ __global__ void __launch_bounds__(BS) fp32_probe_kernel(float *out, int iters) {
 #pragma unroll
             for (int q = 0; q < 16; ++q) {
                 if constexpr (VARIANT == 0) acc[q] = __fmaf_rn(acc[q], a, b);  // reg, reg, reg
-                else acc[q] = __fmaf_rn(acc[q], 0.99999f, b);                  // reg, imm, reg
+                else if constexpr (VARIANT == 1) acc[q] = __fmaf_rn(acc[q], 0.99999f, b);  // reg, imm, reg
             }
+        if constexpr (VARIANT == 2) {  // packed fma.rn.ftz.f32x2: 2 lanes-FMA per thread-instruction
+            unsigned long long pa, pb;
+            asm("mov.b64 %0, {%1, %1};" : "=l"(pa) : "f"(a));
+            asm("mov.b64 %0, {%1, %1};" : "=l"(pb) : "f"(b));
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int q = 0; q < 16; q += 2) {
+                    unsigned long long v;
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "f"(acc[q]), "f"(acc[q + 1]));
+                    asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(v) : "l"(v), "l"(pa), "l"(pb));
+                    asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[q]), "=f"(acc[q + 1]) : "l"(v));
+                }
+        }
     }
     float s = 0.f;
 #pragma unroll
@@ -1346,7 +1361,8 @@ int srnn_assign_uids_static(const uint8_t *dead, int64_t n, int64_t uid_base, in
 int srnn_fp32_probe(float *out, int32_t grid, int32_t block, int32_t iters, void *stream) {
     if (!out || grid < 1 || block < 1 || block > BS) return fail(SRNN_ERR_ARG, "bad probe arguments%s");
     if (iters >= 0) fp32_probe_kernel<0><<<grid, block, 0, (cudaStream_t)stream>>>(out, iters);
-    else fp32_probe_kernel<1><<<grid, block, 0, (cudaStream_t)stream>>>(out, -iters);
+    else if (iters > -(1 << 24)) fp32_probe_kernel<1><<<grid, block, 0, (cudaStream_t)stream>>>(out, -iters);
+    else fp32_probe_kernel<2><<<grid, block, 0, (cudaStream_t)stream>>>(out, -iters - (1 << 24));
     return check_launch("srnn_fp32_probe");
 }
 

@@ -81,9 +81,55 @@ struct Shape : ShapeFn<KIND_, WIDTH_, DEPTH_, AGG_> {
     static constexpr int CS = KIND_ == SRNN_KIND_AGG ? NW / (AGG_ > 0 ? AGG_ : 1) : 0;
 };
 
+// ------------------------------------------------------------------------------------------------ packed FP32
+// Blackwell's packed FP32 instructions (PTX fma/mul .f32x2 -> SASS FFMA2/FMUL2): two IEEE-rn, flush-to-zero
+// lanes per thread-instruction, i.e. the SAME per-lane results as the scalar forms with half the instruction
+// issue and 64-bit register-pair operands (a scalar operand is broadcast to both lanes by the hardware).
+// The two lanes are the two units of a width-2 layer, whose kernel columns W[k][0], W[k][1] are adjacent.
+#ifndef SRNN_PACKED_F32X2
+#define SRNN_PACKED_F32X2 1
+#endif
+typedef unsigned long long f32x2_t;
+SRNN_DEV f32x2_t pack2(float lo, float hi) {
+    f32x2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+SRNN_DEV void unpack2(f32x2_t v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+SRNN_DEV f32x2_t mul2(f32x2_t a, f32x2_t b) {
+    f32x2_t r;
+    asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// 1.0f that ptxas cannot see through.  ptxas (12.9) contracts mul.rn.f32x2 followed by add.rn.f32x2 -- or by an
+// fma.f32x2 whose multiplier is the literal 1 -- into ONE FFMA2, i.e. a single rounding where the reference has
+// two (the explicit .rn does not stop it for the packed forms; it does for scalars).  Multiplying by a 1 that is
+// only known at run time keeps the two roundings and costs the same instruction.
+static __device__ float g_opaque_one = 1.0f;
+SRNN_DEV float opaque_one() { return *reinterpret_cast<volatile float *>(&g_opaque_one); }
+SRNN_DEV f32x2_t fma2(f32x2_t a, f32x2_t b, f32x2_t c) {
+    f32x2_t r;
+    asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
 // ------------------------------------------------------------------------------------------------ dense
 template <int IN, int OUT>
 SRNN_DEV void dense(const float *x, const float *W, float *y) {
+#if SRNN_PACKED_F32X2
+    if constexpr (OUT == 2) {  // R2, both units at once: acc = rn(x0*W0j); acc = fma(xk, Wkj, acc)
+        f32x2_t acc = mul2(pack2(x[0], x[0]), pack2(W[0], W[1]));
+#pragma unroll
+        for (int k = 1; k < IN; ++k) acc = fma2(pack2(x[k], x[k]), pack2(W[2 * k], W[2 * k + 1]), acc);
+        unpack2(acc, y[0], y[1]);
+        return;
+    } else if constexpr (OUT == 1 && IN == 2) {  // R3: the two products in one instruction, adds unfused from +0
+        float p0, p1;
+        unpack2(mul2(pack2(x[0], x[1]), pack2(W[0], W[1])), p0, p1);
+        y[0] = __fadd_rn(__fadd_rn(0.0f, p0), p1);
+        return;
+    }
+#endif
     if constexpr (OUT >= 2) {  // R2
 #pragma unroll
         for (int j = 0; j < OUT; ++j) {
@@ -133,9 +179,28 @@ SRNN_DEV void mlp_forward(const float *w, const float *x, float *y) {
 // out <- f_op(in);  `out` must not alias `in` or `op`.
 // WeightwiseNeuralNetwork.apply_to_weights, code/network.py:265-279
 template <class S>
-SRNN_DEV void ww_apply(const float *op, const float *in, float *out) {
+SRNN_DEV void ww_apply(const float *op, const float *in, float *out, float one) {
     static_for<0, S::NW>([&](auto K) {
         constexpr int k = decltype(K)::value;
+#if SRNN_PACKED_F32X2
+        if constexpr (S::WIDTH == 2) {
+            // first layer with the position codes as compile-time constants; a code of exactly 1 multiplies by the
+            // run-time 1 (see opaque_one: with the literal, points with layer code 1 lost a rounding -- caught by the
+            // parity tests).
+            f32x2_t acc = mul2(pack2(in[k], in[k]), pack2(op[0], op[1]));
+            static_for<0, 3>([&](auto R) {
+                constexpr int r = decltype(R)::value;
+                const f32x2_t W = pack2(op[2 * (r + 1)], op[2 * (r + 1) + 1]);
+                constexpr float code = r == 0 ? S::codeL(k) : (r == 1 ? S::codeR(k) : S::codeC(k));
+                if constexpr (code == 1.0f) acc = fma2(pack2(one, one), W, acc);
+                else acc = fma2(pack2(code, code), W, acc);
+            });
+            float h[2];
+            unpack2(acc, h[0], h[1]);
+            mlp_forward<S, 1>(op, h, &out[k]);
+            return;
+        }
+#endif
         const float x[4] = {in[k], S::codeL(k), S::codeR(k), S::codeC(k)};
         mlp_forward<S>(op, x, &out[k]);
     });
@@ -193,9 +258,10 @@ SRNN_DEV void rnn_forward_seq(const float *op, const float *seq, float *out, flo
         out[t] = x[0];
     });
 }
+// `one` = opaque_one(), fetched once per thread by the caller (hoisted out of the step loops)
 template <class S>
-SRNN_DEV void net_apply(const float *op, const float *in, float *out) {
-    if constexpr (S::KIND == SRNN_KIND_WW) ww_apply<S>(op, in, out);
+SRNN_DEV void net_apply(const float *op, const float *in, float *out, float one) {
+    if constexpr (S::KIND == SRNN_KIND_WW) ww_apply<S>(op, in, out, one);
     else if constexpr (S::KIND == SRNN_KIND_AGG) agg_apply<S>(op, in, out);
     else rnn_forward_seq<S, false>(op, in, out, nullptr);
 }
@@ -232,7 +298,7 @@ SRNN_DEV int classify_with(const float *w, const float *nw, float eps_ge, float 
     if (is_close<S::NW>(nw, w, eps_ge)) return is_zero<S::NW>(w, eps_le) ? SRNN_CLS_FIX_ZERO : SRNN_CLS_FIX_OTHER;
     if (with_fix_sec) {
         float nnw[S::NW];
-        net_apply<S>(w, nw, nnw);  // is_fixpoint(2): the operator stays at w
+        net_apply<S>(w, nw, nnw, opaque_one());  // is_fixpoint(2): the operator stays at w
         if (is_close<S::NW>(nnw, w, eps_ge)) return SRNN_CLS_FIX_SEC;
     }
     return SRNN_CLS_OTHER;
