@@ -319,10 +319,16 @@ template <class S>
 __global__ void __launch_bounds__(BS) init_kernel(float *__restrict__ w, int64_t ld, int64_t n,
                                                   const int32_t *__restrict__ idx, uint64_t seed, uint64_t slot0,
                                                   uint32_t gen, Limits lim) {
-    const int64_t p = (int64_t)blockIdx.x * BS + threadIdx.x;
+    __shared__ __align__(16) float tile[BS * S::NW];
+    const int64_t base = (int64_t)blockIdx.x * BS, p = base + threadIdx.x;
+    float cur[S::NW];
+    if (!idx && ld == S::NW) {  // whole population: coalesced through the tile
+        if (p < n) init_net<S>(seed, slot0 + (uint64_t)p, gen, lim, cur);
+        tile_store<S::NW>(w, ld, base, n, tile, cur);
+        return;
+    }
     if (p >= n) return;
     const int64_t i = idx ? idx[p] : p;
-    float cur[S::NW];
     init_net<S>(seed, slot0 + (uint64_t)i, gen, lim, cur);
     record_store<S::NW>(w, ld, i, cur);
 }
@@ -379,7 +385,7 @@ __global__ void __launch_bounds__(BS) train_kernel(float *__restrict__ w, int64_
                     philox_perm<S::NS>(seed, slot0 + (uint64_t)i, epoch0 + (uint64_t)e, sc.ord, sc.stride);
                 }
             }
-            loss = train_epoch<S>(cur, sc, ordered, lr);
+            loss = train_epoch<S>(cur, sc, ordered, lr, loss_out != nullptr && e == n_epochs - 1);
         }
         if (loss_out) loss_out[i] = loss;
     }
@@ -394,8 +400,15 @@ __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, dou
                                                  int max_steps, Eps eps, uint64_t seed, uint64_t slot0,
                                                  int *__restrict__ ys, int *__restrict__ zs,
                                                  unsigned long long *hist, float *__restrict__ w_out, int64_t ld) {
+    extern __shared__ unsigned int hist_s[];  // [2][max_steps + 1], only when hist != nullptr
     const int64_t i = (int64_t)blockIdx.x * BS + threadIdx.x;
-    if (i >= n) return;
+    const int nbins = 2 * (max_steps + 1);
+    if (hist) {
+        for (int b = threadIdx.x; b < nbins; b += BS) hist_s[b] = 0;
+        __syncthreads();
+    }
+    int tts = 0, taf = 0;
+    if (i < n) {
     float cur[S::NW], nxt[S::NW];
     // vary(), known-fixpoint-variation.py:37-46: float64 perturbation stored as float32
 #pragma unroll
@@ -406,7 +419,6 @@ __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, dou
         cur[k] = (float)(u01d(x.x) < 0.5 ? __dadd_rn(b, mag) : __dsub_rn(b, mag));
     }
     // trial loop :69-82; after each self_attack the fixpoint test's application is the next step's result
-    int tts = 0, taf = 0;
     bool still = true;
     net_apply<S>(cur, cur, nxt, opaque_one());
     for (int st = 0; st < max_steps; ++st) {
@@ -424,11 +436,17 @@ __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, dou
     }
     if (ys) ys[i] = tts;
     if (zs) zs[i] = taf;
-    if (hist) {
-        atomicAdd(&hist[tts], 1ull);
-        atomicAdd(&hist[(max_steps + 1) + taf], 1ull);
-    }
     if (w_out) record_store<S::NW>(w_out, ld, i, cur);
+    if (hist) {  // a few hot bins: count in shared memory, one global atomic per non-empty bin and CTA
+        atomicAdd(&hist_s[tts], 1u);
+        atomicAdd(&hist_s[(max_steps + 1) + taf], 1u);
+    }
+    }
+    if (hist) {
+        __syncthreads();
+        for (int b = threadIdx.x; b < nbins; b += BS)
+            if (hist_s[b]) atomicAdd(&hist[b], (unsigned long long)hist_s[b]);
+    }
 }
 
 // ================================================================================================ K8 soup
@@ -1159,7 +1177,7 @@ int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double s
              int64_t *hist, float *w_out, int64_t ld, void *stream) {
     if (!d || !base_host) return fail(SRNN_ERR_ARG, "desc or base is NULL%s");
     if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
-    if (max_steps < 0) return fail(SRNN_ERR_ARG, "max_steps < 0%s");
+    if (max_steps < 0 || max_steps > 4096) return fail(SRNN_ERR_ARG, "need 0 <= max_steps <= 4096%s");
     Eps e;
     int rc = make_eps(eps, &e);
     if (rc) return rc;
@@ -1168,7 +1186,8 @@ int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double s
 #define BODY(S)                                                                                              \
     if (w_out && ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");       \
     memcpy(bn.v, base_host, sizeof(float) * S::NW);                                                          \
-    kfv_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(bn, n, scale, level, max_steps, e, seed, slot0, \
+    kfv_kernel<S><<<grid_for(n), BS, hist ? sizeof(unsigned int) * 2 * (max_steps + 1) : 0, (cudaStream_t)stream>>>( \
+        bn, n, scale, level, max_steps, e, seed, slot0, \
                                                                 time_to_vergence, time_as_fixpoint,           \
                                                                 (unsigned long long *)hist, w_out, ld);
     SRNN_DISPATCH(d)

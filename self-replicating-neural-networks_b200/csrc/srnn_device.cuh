@@ -503,36 +503,40 @@ struct SgdScratch {
     const float *codes;  // WW: [3][NW] position codes (L, R, C), shared by the block
 };
 
-// Fisher-Yates from 16-bit Philox chunks: for i = n-1 .. 1: j = (chunk * (i+1)) >> 16; swap(i, j)
+// Fisher-Yates from 16-bit Philox chunks: for i = n-1 .. 1: j = (chunk * (i+1)) >> 16; swap(i, j).  Draw d (0-based)
+// uses half (d & 1) of word (d % 8) / 2 of Philox block d / 8.  Fully unrolled: every index but j is a constant.
 template <int NS>
 SRNN_DEV void philox_perm(uint64_t seed, uint64_t slot, uint64_t epoch, uint8_t *ord, int stride) {
 #pragma unroll
     for (int i = 0; i < NS; ++i) ord[i * stride] = (uint8_t)i;
-    U4 x{0, 0, 0, 0};
-    int have = 0;
-    uint32_t blk = 0;
-    for (int i = NS - 1; i >= 1; --i) {
-        if ((have & 7) == 0) x = rng4(seed, ST_PERM, slot, (uint32_t)epoch, ((uint32_t)(epoch >> 32) << 8) | blk++);
-        const uint32_t word = word_of(x, (have & 7) >> 1);
-        const uint32_t chunk = (have & 1) ? (word >> 16) : (word & 0xFFFFu);
-        ++have;
+    constexpr int NDRAW = NS - 1, NBLK = (NDRAW + 7) / 8;
+    U4 x[NBLK > 0 ? NBLK : 1];
+#pragma unroll
+    for (int b = 0; b < NBLK; ++b)
+        x[b] = rng4(seed, ST_PERM, slot, (uint32_t)epoch, ((uint32_t)(epoch >> 32) << 8) | (uint32_t)b);
+    static_for<0, NDRAW>([&](auto D) {
+        constexpr int d = decltype(D)::value, i = NS - 1 - d;
+        constexpr int blk = d / 8, w = (d % 8) / 2;
+        const uint32_t word = w == 0 ? x[blk].x : (w == 1 ? x[blk].y : (w == 2 ? x[blk].z : x[blk].w));
+        const uint32_t chunk = (d & 1) ? (word >> 16) : (word & 0xFFFFu);
         const int j = (int)((chunk * (uint32_t)(i + 1)) >> 16);
         const uint8_t tmp = ord[i * stride];
         ord[i * stride] = ord[j * stride];
         ord[j * stride] = tmp;
-    }
+    });
 }
 
 // One Keras epoch of the student `w` on the samples frozen in sc.tgt; returns the f64 mean sample loss.
 template <class S>
-SRNN_DEV double train_epoch(float *w, const SgdScratch &sc, bool ordered, float lr) {
+SRNN_DEV double train_epoch(float *w, const SgdScratch &sc, bool ordered, float lr, bool want_loss = true) {
     if constexpr (S::KIND == SRNN_KIND_WW) {  // compute_samples, code/network.py:281-289
         double acc = 0.0;
         for (int q = 0; q < S::NW; ++q) {
             const int k = ordered ? (int)sc.ord[q * sc.stride] : q;
             const float v = sc.tgt[k * sc.stride];
             const float x[4] = {v, sc.codes[k], sc.codes[S::NW + k], sc.codes[2 * S::NW + k]};
-            acc = __dadd_rn(acc, (double)mlp_sgd_sample<S>(w, x, &v, lr));
+            const float l = mlp_sgd_sample<S>(w, x, &v, lr);
+            if (want_loss) acc = __dadd_rn(acc, (double)l);   // only the last epoch's loss is ever reported
         }
         return __ddiv_rn(acc, (double)S::NW);
     } else if constexpr (S::KIND == SRNN_KIND_AGG) {  // compute_samples, code/network.py:414-417
