@@ -347,6 +347,7 @@ __device__ __forceinline__ SgdScratch sgd_scratch(unsigned char *smem, int threa
     float *codes = reinterpret_cast<float *>(smem + sizeof(float) * S::NW * threads + (S::NS * threads + 15) / 16 * 16);
     if (threadIdx.x == 0) fill_codes<S>(codes);
     sc.codes = codes;
+    sc.one = opaque_one();
     return sc;
 }
 

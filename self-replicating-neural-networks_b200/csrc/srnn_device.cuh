@@ -387,7 +387,7 @@ SRNN_DEV void init_net(uint64_t seed, uint64_t slot, uint32_t gen, const Limits 
 // code/network.py:613-626): forward, g = (1/n_out) * 2 (out - y), per layer dW = act^T g (single products),
 // g_prev = dense_T(g, W) with the PRE-update W, then W <- rn(W - rn(lr * dW)).  Returns the f32 sample loss.
 template <class S>
-SRNN_DEV float mlp_sgd_sample(float *w, const float *x, const float *y, float lr) {
+SRNN_DEV float mlp_sgd_sample(float *w, const float *x, const float *y, float lr, float one) {
     float act[S::NL + 1][S::MAXU];
 #pragma unroll
     for (int i = 0; i < S::IO; ++i) act[0][i] = x[i];
@@ -397,7 +397,7 @@ SRNN_DEV float mlp_sgd_sample(float *w, const float *x, const float *y, float lr
     });
     constexpr int NO = S::OUTW;
     float g[S::MAXU];
-    const float inv = __fdiv_rn(1.0f, (float)NO);
+    constexpr float inv = 1.0f / (float)NO;   // rn(1/n_out), as TF's mean gradient
     float tot = 0.f;
 #pragma unroll
     for (int j = 0; j < NO; ++j) {
@@ -405,18 +405,38 @@ SRNN_DEV float mlp_sgd_sample(float *w, const float *x, const float *y, float lr
         tot = __fadd_rn(tot, __fmul_rn(dlt, dlt));
         g[j] = __fmul_rn(inv, __fmul_rn(2.0f, dlt));
     }
-    const float loss = __fdiv_rn(tot, (float)NO);
+    // tot / n_out: for a power-of-two n_out the multiplication by 1/n_out is the same rounding and avoids the
+    // division subroutine in the sample loop
+    constexpr bool POW2 = (NO & (NO - 1)) == 0;
+    const float loss = POW2 ? __fmul_rn(tot, 1.0f / (float)NO) : __fdiv_rn(tot, (float)NO);
     static_rfor<S::NL>([&](auto LL) {
         constexpr int l = decltype(LL)::value;
         constexpr int IN = S::in(l), OUT = S::out(l);
         float *W = w + S::off(l);
         float gp[S::MAXU];
         if constexpr (l > 0) dense_T<IN, OUT>(g, W, gp);
+#if SRNN_PACKED_F32X2
+        // W <- rn(W - rn(lr * rn(act*g))) two weights at a time.  The subtraction is spelled fma(1, -step, W) with the
+        // run-time 1 (opaque_one) so that ptxas cannot contract it with the multiply before it.
+        if constexpr (OUT == 2) {
+            const f32x2_t gpair = pack2(g[0], g[1]), nlr = pack2(-lr, -lr), ones = pack2(one, one);
 #pragma unroll
-        for (int i = 0; i < IN; ++i)
+            for (int i = 0; i < IN; ++i) {
+                const f32x2_t step = mul2(nlr, mul2(pack2(act[l][i], act[l][i]), gpair));
+                unpack2(fma2(ones, step, pack2(W[2 * i], W[2 * i + 1])), W[2 * i], W[2 * i + 1]);
+            }
+        } else if constexpr (OUT == 1 && IN == 2) {
+            const f32x2_t step = mul2(pack2(-lr, -lr), mul2(pack2(act[l][0], act[l][1]), pack2(g[0], g[0])));
+            unpack2(fma2(pack2(one, one), step, pack2(W[0], W[1])), W[0], W[1]);
+        } else
+#endif
+        {
 #pragma unroll
-            for (int j = 0; j < OUT; ++j)
-                W[i * OUT + j] = __fsub_rn(W[i * OUT + j], __fmul_rn(lr, __fmul_rn(act[l][i], g[j])));
+            for (int i = 0; i < IN; ++i)
+#pragma unroll
+                for (int j = 0; j < OUT; ++j)
+                    W[i * OUT + j] = __fsub_rn(W[i * OUT + j], __fmul_rn(lr, __fmul_rn(act[l][i], g[j])));
+        }
         if constexpr (l > 0) {
 #pragma unroll
             for (int i = 0; i < IN; ++i) g[i] = gp[i];
@@ -501,6 +521,7 @@ struct SgdScratch {
     uint8_t *ord;
     int stride;       // threads per block (column stride)
     const float *codes;  // WW: [3][NW] position codes (L, R, C), shared by the block
+    float one;        // opaque_one(), fetched once per thread
 };
 
 // Fisher-Yates from 16-bit Philox chunks: for i = n-1 .. 1: j = (chunk * (i+1)) >> 16; swap(i, j).  Draw d (0-based)
@@ -535,7 +556,7 @@ SRNN_DEV double train_epoch(float *w, const SgdScratch &sc, bool ordered, float 
             const int k = ordered ? (int)sc.ord[q * sc.stride] : q;
             const float v = sc.tgt[k * sc.stride];
             const float x[4] = {v, sc.codes[k], sc.codes[S::NW + k], sc.codes[2 * S::NW + k]};
-            const float l = mlp_sgd_sample<S>(w, x, &v, lr);
+            const float l = mlp_sgd_sample<S>(w, x, &v, lr, sc.one);
             if (want_loss) acc = __dadd_rn(acc, (double)l);   // only the last epoch's loss is ever reported
         }
         return __ddiv_rn(acc, (double)S::NW);
@@ -544,7 +565,7 @@ SRNN_DEV double train_epoch(float *w, const SgdScratch &sc, bool ordered, float 
 #pragma unroll
         for (int k = 0; k < S::NW; ++k) t[k] = sc.tgt[k * sc.stride];
         agg_means<S>(t, agg);
-        return (double)mlp_sgd_sample<S>(w, agg, agg, lr);
+        return (double)mlp_sgd_sample<S>(w, agg, agg, lr, sc.one);
     } else {
         float t[S::NW];
 #pragma unroll
