@@ -352,7 +352,12 @@ def main():
         line.update(extra)
         if world == 1:
             v, cores, sample = cpu_port_rate(1 << 20, args.cpu_seconds)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+            from oracle import numpy_twin
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                                    "reference_structured_1core": numpy_twin.self_applications_per_second(),
+                                    "reference_structured_note": "per-object Python loops of code/network.py:239-279 with a "
+                                    "NumPy dot instead of model.predict, one core; the reference's own Keras/TF1 path is "
+                                    "unavailable on this box"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
