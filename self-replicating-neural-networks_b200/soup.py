@@ -403,6 +403,37 @@ class PopulationSoup:
         base, self.next_uid = uid_base_of(self.rank, counts, self.next_uid)
         self.backend.assign_uids(self.dead, self.uid, base, self._uid_tmp, self._n_dead)
 
+    # ---- checkpoint / resume (the reference can only dill-dump finished experiments, code/experiment.py:56-59)
+    def state_dict(self):
+        """Everything needed to continue this rank's shard bit-for-bit: records, uids, clocks, parameters."""
+        return dict(kind=self.desc.kind, width=self.desc.width, depth=self.desc.depth, aggregates=self.desc.aggregates,
+                    size=self.size, world=self.world, rank=self.rank, seed=self.seed, time=self.time,
+                    next_uid=self.next_uid, params=dict(self.params), w=self.w.detach().cpu().clone(),
+                    uid=self.uid.detach().cpu().clone())
+
+    def load_state_dict(self, state):
+        for key in ("kind", "width", "depth", "size", "world", "rank"):
+            have = getattr(self.desc, key) if key in ("kind", "width", "depth") else getattr(self, key)
+            if int(state[key]) != int(have):
+                raise ValueError("checkpoint %s=%r does not match this soup (%r)" % (key, state[key], have))
+        self.seed, self.time, self.next_uid = int(state["seed"]), int(state["time"]), int(state["next_uid"])
+        self.params.update(state["params"])
+        self.w.copy_(state["w"])
+        self.uid.copy_(state["uid"])
+        if self._peer is not None:
+            self._peer[1].barrier()
+        return self
+
+    def save(self, path):
+        """One file per rank: `path` gets a .rank{r} suffix when the soup is sharded."""
+        import torch
+        torch.save(self.state_dict(), path if self.world == 1 else "%s.rank%d" % (path, self.rank))
+
+    def load(self, path):
+        import torch
+        return self.load_state_dict(torch.load(path if self.world == 1 else "%s.rank%d" % (path, self.rank),
+                                               weights_only=False))
+
     def count(self, with_fix_sec=True):
         """Soup.count over the whole (possibly sharded) population."""
         import torch.distributed as dist

@@ -336,3 +336,25 @@ def test_population_soup_single_rank(api):
     rc = oracle.classify(do, ref, 1e-4)[1]
     assert list(c.values()) == rc.tolist()
     assert ps.next_uid >= n and int(ps.uid.max().item()) == ps.next_uid - 1
+
+
+def test_population_soup_checkpoint_resume(api, tmp_path):
+    """Stop after 3 generations, save, resume in a new object: identical to an uninterrupted run."""
+    network, soup_mod, _ = api
+    import srnn_engine as eng
+    kw = dict(seed=9, attacking_rate=0.2, learn_from_rate=0.2, train=1, remove_divergent=True, remove_zero=True)
+    a = soup_mod.PopulationSoup(eng.KIND_AGG, 3000, aggregates=4, **kw).seed_particles()
+    a.track_uids = True
+    a.evolve(6)
+    b = soup_mod.PopulationSoup(eng.KIND_AGG, 3000, aggregates=4, **kw).seed_particles()
+    b.track_uids = True
+    b.evolve(3)
+    b.save(str(tmp_path / "soup.pt"))
+    c = soup_mod.PopulationSoup(eng.KIND_AGG, 3000, aggregates=4, **kw)
+    c.track_uids = True
+    c.load(str(tmp_path / "soup.pt"))
+    assert c.time == 3
+    c.evolve(3)
+    assert_same_weights(c.local.numpy(), a.local.numpy())
+    assert np.array_equal(c.uid.cpu().numpy(), a.uid.cpu().numpy()) and c.next_uid == a.next_uid
+

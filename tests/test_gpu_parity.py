@@ -365,3 +365,60 @@ def test_full_size_properties(eng):
     assert torch.equal(cnt, parts) and int(cnt.sum()) == n
     rc, rcnt = oracle.classify(do, sample, 1e-4)
     assert np.array_equal(cls[5::1024].cpu().numpy(), rc)
+
+
+# ---------------------------------------------------------------- edge cases of the C ABI
+def test_empty_and_invalid_calls(eng):
+    """n = 0 is a no-op; bad arguments are status codes with a message, never a crash or a silent fallback."""
+    import ctypes as C
+    import torch
+    lib = eng.lib()
+    dg, _ = both(eng, (0, 2, 2, 0))
+    w = torch.zeros((4, 14), dtype=torch.float32, device="cuda")
+    p = C.c_void_p(w.data_ptr())
+    assert lib.srnn_self_apply(C.byref(dg), p, C.c_int64(14), C.c_int64(0), C.c_int32(5), C.c_int32(0), C.c_double(1e-4),
+                               C.c_int32(1), None, None, None, None, None) == 0
+    assert lib.srnn_classify(C.byref(dg), p, C.c_int64(14), C.c_int64(0), C.c_double(1e-4), C.c_int32(1), None, None, None,
+                             None) == 0
+    # record stride smaller than the record
+    assert lib.srnn_self_apply(C.byref(dg), p, C.c_int64(13), C.c_int64(4), C.c_int32(1), C.c_int32(0), C.c_double(1e-4),
+                               C.c_int32(1), None, None, None, None, None) == 1
+    assert b"stride" in lib.srnn_last_error_string()
+    # NULL arena
+    assert lib.srnn_self_apply(C.byref(dg), None, C.c_int64(14), C.c_int64(4), C.c_int32(1), C.c_int32(0), C.c_double(1e-4),
+                               C.c_int32(1), None, None, None, None, None) == 1
+    # epsilon below FLT_MIN is refused where predicates are evaluated
+    cls = torch.zeros(4, dtype=torch.uint8, device="cuda")
+    assert lib.srnn_classify(C.byref(dg), p, C.c_int64(14), C.c_int64(4), C.c_double(1e-60), C.c_int32(1),
+                             C.c_void_p(cls.data_ptr()), None, None, None) == 1
+    assert b"epsilon" in lib.srnn_last_error_string()
+    # unknown run mode / negative step count
+    assert lib.srnn_self_apply(C.byref(dg), p, C.c_int64(14), C.c_int64(4), C.c_int32(1), C.c_int32(7), C.c_double(1e-4),
+                               C.c_int32(1), None, None, None, None, None) == 1
+    assert lib.srnn_self_apply(C.byref(dg), p, C.c_int64(14), C.c_int64(4), C.c_int32(-1), C.c_int32(0), C.c_double(1e-4),
+                               C.c_int32(1), None, None, None, None, None) == 1
+    # a shape that is valid but not instantiated
+    d2 = eng.make_desc(0, 4, 3)
+    w2 = torch.zeros((4, d2.n_weights), dtype=torch.float32, device="cuda")
+    assert lib.srnn_self_apply(C.byref(d2), C.c_void_p(w2.data_ptr()), C.c_int64(d2.n_weights), C.c_int64(4), C.c_int32(1),
+                               C.c_int32(0), C.c_double(1e-4), C.c_int32(1), None, None, None, None, None) == 2
+    torch.cuda.synchronize()
+    assert float(w.abs().sum()) == 0.0
+
+
+def test_nan_inf_are_states_not_errors(eng):
+    """A NaN attacker infects its victim; infinities propagate with IEEE semantics."""
+    dg, do = both(eng, (0, 2, 2, 0))
+    w = glorot_population((0, 2, 2, 0), 64, seed=3)
+    w[0, 3] = np.nan
+    w[1, 0] = np.inf
+    w[2, 13] = -np.inf
+    pop = eng.Population.from_numpy(dg, w)
+    pop.attack(np.array([0, 1, 2]), np.array([10, 11, 12]))
+    ref = w.copy()
+    oracle.apply(do, ref, [0, 1, 2], ref, [10, 11, 12], ref, [10, 11, 12], 3)
+    assert_same_weights(pop.numpy(), ref)
+    assert not np.isfinite(pop.numpy()[10:13]).all(axis=1).any()
+    cls = pop.classify(1e-4)[0].cpu().numpy()
+    assert (cls[[0, 1, 2, 10, 11, 12]] == 0).all()
+
