@@ -42,8 +42,8 @@ FLOP_PER_SELF_APP = 392.0       # 14 points x 14 MAC x 2
 FP32_INSTR_PER_SELF_APP = 224.0  # FMA-pipe lane-ops in the pinned operation order: 14 x (8 FMA + 6 MUL + 2 ADD)
 BYTES_PER_NET = 112.0           # 56 B read + 56 B write per resident episode
 # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel at 2^24 nets
-# (profiles/r01_k1_self_apply_fixed_ncu_summary.csv): 941.3 MB + 881.2 MB per launch
-NCU_TRAFFIC_BYTES_PER_NET = (941.286656e6 + 881.191168e6) / (1 << 24)
+# (profiles/r01_k1_self_apply_fixed_packed_ncu_summary.csv): 940.3 MB + 880.5 MB per launch
+NCU_TRAFFIC_BYTES_PER_NET = (940.291584e6 + 880.501760e6) / (1 << 24)
 METRIC = "net self-applications/sec"
 UNIT = "self-applications/s"
 
@@ -383,7 +383,7 @@ def main():
             "gpu_launches": K,
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": NCU_TRAFFIC_BYTES_PER_NET * n,
-                         "traffic_source": "ncu --set full, profiles/r01_k1_self_apply_fixed_ncu_summary.csv "
+                         "traffic_source": "ncu --set full, profiles/r01_k1_self_apply_fixed_packed_ncu_summary.csv "
                                            "(algorithmic bytes per launch = 112 B x nets)",
                          "kernel": "self_apply_fixed_kernel<WW(2,2)>", "kernel_ms": kern_ms,
                          "peak_source": "FFMA-only probe kernel measured live (MEASURED_PEAKS.json has no FP32 entry)",
