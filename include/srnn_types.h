@@ -64,7 +64,8 @@ typedef struct srnn_soup_params {
     double  epsilon;             /* particles' params['epsilon']                  */
     float   lr;                  /* Keras SGD default 0.01                        */
     int32_t perm_mode;           /* SRNN_PERM_NONE or SRNN_PERM_PHILOX            */
-    int32_t engine_path;         /* srnn_soup_sync only: 0 auto, 1 fused single kernel, 2 multi-pass (same results) */
+    int32_t engine_path;         /* srnn_soup_sync*: 0 auto, 1 fused kernel per generation, 2 multi-pass, 3 persistent
+                                    cooperative kernel for srnn_soup_sync_run (all give the same results) */
 } srnn_soup_params;
 
 #define SRNN_MAX_WEIGHTS 64      /* per-net weight count supported by the generic code paths */

@@ -15,6 +15,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 
@@ -35,6 +36,8 @@ constexpr int SOUP_BS = SRNN_SOUP_BS;
 // engine_path = 0 (auto) takes the fused single kernel; the multi-pass (globally compacted) generation is kept
 // selectable (engine_path = 2): it measured 0.91 / 1.33 ms against 0.73 / 1.18 ms for the fused kernel at 10 M particles.
 constexpr int64_t SOUP_MULTIPASS_MIN = INT64_MAX;
+// largest unsharded soup the opt-in persistent cooperative variant of srnn_soup_sync_run accepts
+constexpr int64_t SOUP_PERSISTENT_MAX = 1 << 20;
 
 // ------------------------------------------------------------------------------------------------ errors
 static thread_local char g_err[512] = "";
@@ -71,17 +74,19 @@ static int make_eps(double eps, Eps *e) {
 // 17 -> LDS.32 at an odd stride).
 template <int NW> struct TileVec { static constexpr int V = NW % 4 == 0 ? 4 : (NW % 2 == 0 ? 2 : 1); };
 
-template <int NT>
+// CG = true: loads bypass L1 (ld.global.cg) -- for the persistent soup kernel, which re-reads arenas that other CTAs
+// rewrote earlier in the SAME launch.
+template <int NT, bool CG = false>
 __device__ __forceinline__ void flat_copy(float *__restrict__ dst, const float *__restrict__ src, int total) {
     const int tid = threadIdx.x;
     if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
         const int nv = total >> 2;
         const float4 *s4 = reinterpret_cast<const float4 *>(src);
         float4 *d4 = reinterpret_cast<float4 *>(dst);
-        for (int e = tid; e < nv; e += NT) d4[e] = s4[e];
-        for (int e = (nv << 2) + tid; e < total; e += NT) dst[e] = src[e];
+        for (int e = tid; e < nv; e += NT) d4[e] = CG ? __ldcg(s4 + e) : s4[e];
+        for (int e = (nv << 2) + tid; e < total; e += NT) dst[e] = CG ? __ldcg(src + e) : src[e];
     } else {
-        for (int e = tid; e < total; e += NT) dst[e] = src[e];
+        for (int e = tid; e < total; e += NT) dst[e] = CG ? __ldcg(src + e) : src[e];
     }
 }
 template <int NW>
@@ -121,15 +126,15 @@ __device__ __forceinline__ void tile_put(float *tile, int r, const float *reg) {
     }
 }
 // whole-tile staging, HBM -> shared (any record stride)
-template <int NW, int NT>
+template <int NW, int NT, bool CG = false>
 __device__ __forceinline__ void tile_stage_in(const float *__restrict__ w, int64_t ld, int64_t base, int64_t n, float *tile) {
     const int cnt = (int)min((int64_t)NT, n - base);
     if (ld == NW) {
-        flat_copy<NT>(tile, w + base * NW, cnt * NW);
+        flat_copy<NT, CG>(tile, w + base * NW, cnt * NW);
     } else if ((int)threadIdx.x < cnt) {
         const float *src = w + (base + threadIdx.x) * ld;
 #pragma unroll
-        for (int k = 0; k < NW; ++k) tile[threadIdx.x * NW + k] = __ldg(src + k);
+        for (int k = 0; k < NW; ++k) tile[threadIdx.x * NW + k] = CG ? __ldcg(src + k) : __ldg(src + k);
     }
 }
 template <int NW, int NT>
@@ -584,9 +589,9 @@ __device__ __forceinline__ const float *shard_record(const ShardTable &t, int64_
     return t.base[r] + (g - (int64_t)r * t.len) * ld;
 }
 
-template <class S>
-__device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t snap_ld, const int32_t *__restrict__ head,
-                                             const int32_t *__restrict__ next, int64_t v, float *cur);
+template <class S, bool CG = false>
+__device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t snap_ld, const int32_t *head,
+                                             const int32_t *next, int64_t v, float *cur);
 
 // phase B.  The CTA keeps its 256 records in shared memory and runs the generation as a sequence of phases; the
 // rare events of each phase (a particle that is attacked: ~10 %, one that learns: ~10 %, one that dies) are
@@ -595,13 +600,12 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 #ifndef SRNN_SOUP_MINB
 #define SRNN_SOUP_MINB 10
 #endif
-template <class S, int SBS>
-__global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_sync_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
-                                                       int64_t n_total, float *__restrict__ w_out, int64_t out_ld,
-                                                       int64_t slot0, int64_t n, SoupP p, uint64_t seed, uint64_t gen,
-                                                       Limits lim, const int32_t *__restrict__ head,
-                                                       const int32_t *__restrict__ next, uint8_t *action,
-                                                       double *loss, uint8_t *dead_out) {
+template <class S, int SBS, bool CG>
+__device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const ShardTable &snap, const float *own,
+                                                     int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld,
+                                                     int64_t slot0, int64_t n, const SoupP &p, uint64_t seed, uint64_t gen,
+                                                     const Limits &lim, const int32_t *head, const int32_t *next,
+                                                     uint8_t *action, double *loss, uint8_t *dead_out) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int NW = S::NW;
     __shared__ __align__(16) float tile[SBS * NW];
@@ -609,23 +613,23 @@ __global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_sync_kernel(ShardTab
     __shared__ uint16_t queue[SBS];
     __shared__ int q_len;
     const int tid = threadIdx.x;
-    const int64_t base = (int64_t)blockIdx.x * SBS, i = base + tid;
+    const int64_t base = tile_idx * SBS, i = base + tid;
     const bool active = i < n;
     SgdScratch sc = sgd_scratch<S>(smem, SBS);
     // ---- stage the CTA's own records (flat vector copy when packed)
-    tile_stage_in<NW, SBS>(own, snap_ld, base, n, tile);
+    tile_stage_in<NW, SBS, CG>(own, snap_ld, base, n, tile);
     if (tid == 0) q_len = 0;
     int64_t at = -1, lr = -1;
     if (active) soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at, &lr);
     __syncthreads();
     // ---- phase 1: particles hit by attackers (code/soup.py:56-61 seen from the victim)
-    if (active && head[i] >= 0) queue[atomicAdd(&q_len, 1)] = (uint16_t)tid;
+    if (active && (CG ? __ldcg(head + i) : head[i]) >= 0) queue[atomicAdd(&q_len, 1)] = (uint16_t)tid;
     __syncthreads();
     if (tid < q_len) {
         const int v = queue[tid];
         float cur[NW];
         tile_get<NW>(tile, v, cur);
-        attack_chain<S>(snap, snap_ld, head, next, base + v, cur);
+        attack_chain<S, CG>(snap, snap_ld, head, next, base + v, cur);
         tile_put<NW>(tile, v, cur);
     }
     __syncthreads();
@@ -644,7 +648,7 @@ __global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_sync_kernel(ShardTab
         tile_get<NW>(tile, v, cur);
         const float *rec = shard_record(snap, snap_ld, lrn_s[v]);
 #pragma unroll
-        for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = __ldg(rec + k);
+        for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = CG ? __ldcg(rec + k) : __ldg(rec + k);
         for (int e = 0; e < sev; ++e) {
             if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + base + v), ep + (uint64_t)e, sc.ord, sc.stride);
             train_epoch<S>(cur, sc, ordered, p.lr);
@@ -692,6 +696,72 @@ __global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_sync_kernel(ShardTab
     __syncthreads();
     // ---- write the new generation
     tile_stage_out<NW, SBS>(w_out, out_ld, base, n, tile);
+}
+
+template <class S, int SBS>
+__global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_sync_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
+                                                       int64_t n_total, float *__restrict__ w_out, int64_t out_ld,
+                                                       int64_t slot0, int64_t n, SoupP p, uint64_t seed, uint64_t gen,
+                                                       Limits lim, const int32_t *__restrict__ head,
+                                                       const int32_t *__restrict__ next, uint8_t *action,
+                                                       double *loss, uint8_t *dead_out) {
+    soup_tile_generation<S, SBS, false>(blockIdx.x, snap, own, snap_ld, n_total, w_out, out_ld, slot0, n, p, seed, gen, lim,
+                                        head, next, action, loss, dead_out);
+}
+
+// Persistent variant for small, launch-bound soups (one GPU, whole population): the generation loop runs ON the device.
+// All CTAs are co-resident (cooperative launch) and meet at a grid barrier twice per generation:
+//   [pairing draws -> attack lists]  barrier  [tile generations, reset own list heads]  barrier
+// so 1000 generations of a 100k-particle soup are ONE launch instead of 3000 stream operations.  Arenas written
+// earlier in the same launch are re-read with L1-bypassing loads (CG).
+__device__ __forceinline__ void grid_barrier(unsigned *counter, unsigned &target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        target += gridDim.x;
+        __threadfence();
+        atomicAdd(counter, 1u);
+        while (*reinterpret_cast<volatile unsigned *>(counter) < target) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+template <class S, int SBS>
+__global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_persistent_kernel(float *w_a, float *w_b, int64_t ld, int64_t n,
+                                                                             SoupP p, uint64_t seed, uint64_t gen0,
+                                                                             int n_gens, Limits lim, int32_t *head,
+                                                                             int32_t *next, uint8_t *action,
+                                                                             uint8_t *dead_out, unsigned *barrier) {
+    unsigned target = 0;
+    const int64_t gtid = (int64_t)blockIdx.x * SBS + threadIdx.x, gsize = (int64_t)gridDim.x * SBS;
+    const int64_t n_tiles = (n + SBS - 1) / SBS;
+    for (int64_t i = gtid; i < n; i += gsize) head[i] = -1;
+    grid_barrier(barrier, target);
+    for (int g = 0; g < n_gens; ++g) {
+        const uint64_t gen = gen0 + (uint64_t)g;
+        float *src = (g & 1) ? w_b : w_a, *dst = (g & 1) ? w_a : w_b;
+        if (p.attacking_rate > 0.0) {
+            for (int64_t a = gtid; a < n; a += gsize) {
+                int64_t at, lr;
+                soup_draw(p, seed, (uint64_t)a, gen, n, &at, &lr);
+                if (at >= 0) next[a] = atomicExch(&head[at], (int32_t)a);
+            }
+        }
+        grid_barrier(barrier, target);
+        ShardTable tab;
+        tab.base[0] = src;
+        tab.len = n;
+        tab.n = 1;
+        const bool last = g == n_gens - 1;
+        for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            soup_tile_generation<S, SBS, true>(t, tab, src, ld, n, dst, ld, 0, n, p, seed, gen, lim, head, next,
+                                               last ? action : nullptr, nullptr, last ? dead_out : nullptr);
+            const int64_t i = t * SBS + threadIdx.x;
+            if (i < n) head[i] = -1;   // consumed: ready for the next generation's lists
+            __syncthreads();           // the shared tile is reused by the next tile of this CTA
+        }
+        grid_barrier(barrier, target);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------- multi-pass path
@@ -746,19 +816,19 @@ __global__ void __launch_bounds__(EV_BS) soup_events_kernel(SoupP p, uint64_t se
 }
 
 // apply the attackers of local particle v (list head[v] -> next[...]) to `cur` in ascending attacker index
-template <class S>
-__device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t snap_ld, const int32_t *__restrict__ head,
-                                             const int32_t *__restrict__ next, int64_t v, float *cur) {
+template <class S, bool CG>
+__device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t snap_ld, const int32_t *head,
+                                             const int32_t *next, int64_t v, float *cur) {
     int32_t last = -1;
     for (;;) {  // lists are short (Poisson(attacking_rate)): select the next-larger attacker by rescanning
         int32_t best = 0x7fffffff, larger = 0;
-        for (int32_t a = head[v]; a >= 0; a = next[a])
+        for (int32_t a = CG ? __ldcg(head + v) : head[v]; a >= 0; a = CG ? __ldcg(next + a) : next[a])
             if (a > last) { ++larger; if (a < best) best = a; }
         if (larger == 0) break;
         float op[S::NW], res[S::NW];
         const float *rec = shard_record(snap, snap_ld, best);
 #pragma unroll
-        for (int k = 0; k < S::NW; ++k) op[k] = __ldg(rec + k);
+        for (int k = 0; k < S::NW; ++k) op[k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
         net_apply<S>(op, cur, res, opaque_one());
 #pragma unroll
         for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
@@ -1232,6 +1302,7 @@ static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, con
     cudaStream_t st = (cudaStream_t)stream;
     cudaError_t ce = cudaMemsetAsync(head, 0xFF, sizeof(int32_t) * (size_t)n, st);
     if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    if (q.path < 0 || q.path > 3) return fail(SRNN_ERR_ARG, "engine_path must be 0..3%s");
     const bool multipass = q.path == 2 || (q.path == 0 && n >= SOUP_MULTIPASS_MIN);
     if (multipass) {
         int32_t *victims = next + n_total, *learners = victims + n;
@@ -1308,6 +1379,41 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
                        uint64_t seed, uint64_t gen0, int32_t n_gens, int32_t *scratch, uint8_t *action, uint8_t *dead,
                        void *stream) {
     if (n_gens < 0) return fail(SRNN_ERR_ARG, "n_gens < 0%s");
+    if (n_gens == 0 || n <= 0) return SRNN_OK;
+    if (d && p && scratch && w_a && w_b && n <= SOUP_PERSISTENT_MAX && p->engine_path == 3) {
+        // opt-in (engine_path = 3): one cooperative launch runs all generations on the device.  Measured on a B200 it
+        // buys little -- 22 vs 23.5 us per generation at 100k particles, slower at 1 M -- because a generation is bound
+        // by the latency of its serial phases inside each tile, not by launch overhead; so it is not the default.
+        if (n >= 0x7fffffffLL) return fail(SRNN_ERR_ARG, "n too large%s");
+        if (w_a == w_b) return fail(SRNN_ERR_ARG, "w_a must not alias w_b%s");
+        SoupP q;
+        int rc = make_soup(p, &q);
+        if (rc) return rc;
+        Limits lim = make_limits(d);
+        int32_t *head = scratch, *next = scratch + n;
+        unsigned *barrier = reinterpret_cast<unsigned *>(scratch + 5 * n + 8);
+        cudaStream_t st = (cudaStream_t)stream;
+        cudaError_t ce = cudaMemsetAsync(barrier, 0, sizeof(unsigned), st);
+        if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+        int nn_gens = n_gens;
+#define BODY(S)                                                                                              \
+    if (ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");                \
+    constexpr int SBS = SOUP_BS;                                                                             \
+    const size_t sm = sgd_smem_bytes<S>(SBS);                                                                \
+    int per_sm = 0, dev = 0, sms = 0;                                                                        \
+    cudaGetDevice(&dev);                                                                                     \
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);                                       \
+    ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, soup_persistent_kernel<S, SBS>, SBS, sm);    \
+    if (ce != cudaSuccess || per_sm < 1) return fail(SRNN_ERR_CUDA, "occupancy query: %s", cudaGetErrorString(ce)); \
+    const int64_t tiles = (n + SBS - 1) / SBS;                                                               \
+    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)per_sm * sms);                         \
+    void *args[] = {&w_a, &w_b, &ld, &n, &q, &seed, &gen0, &nn_gens, &lim, &head, &next, &action, &dead, &barrier}; \
+    ce = cudaLaunchCooperativeKernel((void *)soup_persistent_kernel<S, SBS>, dim3(grid), dim3(SBS), args, sm, st); \
+    if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cooperative launch: %s", cudaGetErrorString(ce));
+        SRNN_DISPATCH(d)
+#undef BODY
+        return check_launch("srnn_soup_sync_run (persistent)");
+    }
     for (int32_t g = 0; g < n_gens; ++g) {   // generation gen0+g reads one arena and writes the other
         float *src = (g & 1) ? w_b : w_a, *dst = (g & 1) ? w_a : w_b;
         int rc = srnn_soup_sync(d, p, src, ld, n, dst, ld, 0, n, seed, gen0 + (uint64_t)g, scratch, action, nullptr, dead,

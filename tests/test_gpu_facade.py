@@ -358,3 +358,26 @@ def test_population_soup_checkpoint_resume(api, tmp_path):
     assert_same_weights(c.local.numpy(), a.local.numpy())
     assert np.array_equal(c.uid.cpu().numpy(), a.uid.cpu().numpy()) and c.next_uid == a.next_uid
 
+
+@pytest.mark.parametrize("kind,n,gens", [(0, 5000, 7), (1, 3000, 4), (2, 2000, 3), (0, 300_000, 5)])
+def test_persistent_soup_equals_per_generation_launches(api, kind, n, gens):
+    """engine_path=3: evolve(k) of an unsharded soup as ONE persistent cooperative launch (grid barriers between
+    generations); it must equal k single-generation launches bit for bit -- also with more tiles than resident CTAs."""
+    network, soup_mod, _ = api
+    import srnn_engine as eng
+    kw = dict(seed=21, aggregates=4 if kind == 1 else 0, attacking_rate=0.3, learn_from_rate=0.2, train=1,
+              learn_from_severity=2, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+    a = soup_mod.PopulationSoup(kind, n, engine_path=3, **kw).seed_particles()
+    a.evolve(gens)                                        # persistent kernel
+    b = soup_mod.PopulationSoup(kind, n, engine_path=1, **kw).seed_particles()
+    for _ in range(gens):
+        b.evolve(1)                                       # one fused launch per generation
+    assert a.time == b.time == gens
+    assert_same_weights(a.local.numpy(), b.local.numpy())
+    assert np.array_equal(a.action.cpu().numpy(), b.action.cpu().numpy())
+    assert np.array_equal(a.dead.cpu().numpy(), b.dead.cpu().numpy())
+    a.evolve(2)                                           # odd / even ping-pong continues correctly
+    b.evolve(1)
+    b.evolve(1)
+    assert_same_weights(a.local.numpy(), b.local.numpy())
+
