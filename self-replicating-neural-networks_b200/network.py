@@ -99,7 +99,11 @@ class _ModelView:
     """What get_model() returns: the slice of the Keras Sequential API user code touches on a built model."""
 
     def __init__(self, net):
-        self._net = net
+        self._ref = weakref.ref(net)     # no reference cycle: a dead net frees its arena row by refcount alone
+
+    @property
+    def _net(self):
+        return self._ref()
 
     def get_weights(self):
         return self._net.get_weights()
