@@ -1,11 +1,17 @@
-"""experiment -- host-side mirror of the reference's code/experiment.py.
+"""experiment -- host-side stand-in for the reference's code/experiment.py.
 
-Experiment is file-system bookkeeping (directory, log, dill dumps) and stays plain Python, as in the
-reference.  The two hot loops of this module -- FixpointExperiment.run_net (code/experiment.py:70-77) and
-count (:79-91) -- are ONE kernel launch each here: the stop rule, the per-step trajectory and the 5-way
-classification run on the device (srnn_self_apply mode=SRNN_RUN_UNTIL, srnn_classify).
+What lives here is bookkeeping, and it stays plain Python as in the reference: an experiment owns a directory
+`experiments/exp-<name>-<id>-<iteration>/` (relative to the working directory), a list of log messages and
+dill dumps of whatever the script hands to save().  The directory layout, the file names (`log.txt`,
+`<key>.dill`, `experiment.dill`) and the attributes that end up inside the pickles (experiment_id,
+experiment_name, next_iteration, log_messages, historical_particles, counters, ...) are kept, because the
+reference's plotting scripts read them back.
 
-Star-import surface kept for the setups: os, time, dill, tqdm, copy (code/experiment.py:1-5).
+The two hot loops of this module are NOT Python here: FixpointExperiment.run_net (code/experiment.py:70-77) and
+count (:79-91) are one kernel launch each -- the stop rule, the per-step trajectory and the 5-way classification
+run on the device (srnn_self_apply with SRNN_RUN_UNTIL, srnn_classify).
+
+Names re-exported for `from experiment import *`, as the setups expect: os, time, dill, tqdm, copy.
 """
 import copy
 import os
@@ -17,29 +23,40 @@ from tqdm import tqdm
 __all__ = ["os", "time", "dill", "tqdm", "copy", "Experiment", "FixpointExperiment", "MixedFixpointExperiment",
            "SoupExperiment", "IdentLearningExperiment"]
 
+_CLASS_LABELS = ("divergent", "fix_zero", "fix_other", "fix_sec", "other")
+_UNPICKLED_ATTRS = ("particles", "historical_particles")     # live nets do not pickle; their `states` lists do
+
+
+def _dill_to(path, obj):
+    with open(path, "wb") as handle:
+        dill.dump(obj, handle)
+
 
 class Experiment:
-    """Context manager that owns `experiments/exp-{name}-{id}-{it}/`, a log and dill dumps
-    (code/experiment.py:8-59)."""
-
-    @staticmethod
-    def from_dill(path):
-        with open(path, "rb") as fh:
-            return dill.load(fh)
+    """`with Experiment('name') as exp:` creates the directory on entry and writes `experiment.dill` + `log.txt`
+    on exit (also when the block raises, like the reference)."""
 
     def __init__(self, name=None, ident=None):
-        self.experiment_id = "{}_{}".format(ident or "", time.time())
-        self.experiment_name = name or "unnamed_experiment"
+        self.experiment_id = "%s_%s" % (ident or "", time.time())
+        self.experiment_name = name if name else "unnamed_experiment"
         self.next_iteration = 0
         self.log_messages = []
         self.historical_particles = {}
 
+    # -- loading ---------------------------------------------------------------------------------------
+    @staticmethod
+    def from_dill(path):
+        with open(path, "rb") as handle:
+            return dill.load(handle)
+
+    # -- context manager -------------------------------------------------------------------------------
+    def _directory_name(self):
+        return "exp-%s-%s-%s" % (self.experiment_name, self.experiment_id, self.next_iteration)
+
     def __enter__(self):
-        leaf = "exp-{name}-{id}-{it}".format(name=self.experiment_name, id=self.experiment_id,
-                                             it=self.next_iteration)
-        self.dir = os.path.join("experiments", leaf)
-        os.makedirs(self.dir)                       # must not pre-exist, as in the reference
-        print("** created {dir} **".format(dir=self.dir))
+        self.dir = os.path.join("experiments", self._directory_name())
+        os.makedirs(self.dir)            # an existing directory is an error, as in the reference
+        print("** created %s **" % self.dir)
         return self
 
     def __exit__(self, exc_type, exc_value, traceback):
@@ -47,68 +64,69 @@ class Experiment:
         self.save_log()
         self.next_iteration += 1
 
-    def log(self, message, **kwargs):
+    # -- logging ---------------------------------------------------------------------------------------
+    def log(self, message, **print_kwargs):
         self.log_messages.append(message)
-        print(message, **kwargs)
+        print(message, **print_kwargs)
 
     def save_log(self, log_name="log"):
-        path = os.path.join(self.dir, "{name}.txt".format(name=log_name))
-        with open(path, "w") as fh:
-            for message in self.log_messages:
-                print(str(message), file=fh)
+        target = os.path.join(self.dir, log_name + ".txt")
+        with open(target, "w") as handle:
+            handle.writelines(str(message) + "\n" for message in self.log_messages)
 
+    # -- pickling --------------------------------------------------------------------------------------
     def __copy__(self):
-        twin = Experiment(name=self.experiment_name)
-        twin.__dict__ = {k: v for k, v in self.__dict__.items() if k not in ("particles", "historical_particles")}
-        return twin
+        clone = Experiment(name=self.experiment_name)
+        clone.__dict__ = {key: value for key, value in vars(self).items() if key not in _UNPICKLED_ATTRS}
+        return clone
 
     def without_particles(self):
-        """Picklable copy: particles replaced by their `states` lists (code/experiment.py:50-54)."""
-        twin = copy.copy(self)
-        twin.historical_particles = {uid: p.states for uid, p in self.historical_particles.items()}
-        return twin
+        """A shallow copy whose historical_particles maps uid -> list of state dicts."""
+        clone = copy.copy(self)
+        clone.historical_particles = {uid: particle.states for uid, particle in self.historical_particles.items()}
+        return clone
 
-    def save(self, **kwargs):
-        for name, value in kwargs.items():
-            with open(os.path.join(self.dir, "{name}.dill".format(name=name)), "wb") as fh:
-                dill.dump(value, fh)
+    def save(self, **named_objects):
+        for key, obj in named_objects.items():
+            _dill_to(os.path.join(self.dir, key + ".dill"), obj)
 
 
 class FixpointExperiment(Experiment):
+    """Adds the class counters and the two loops every fixpoint script uses."""
 
     def __init__(self, **kwargs):
-        kwargs.setdefault("name", self.__class__.__name__)
+        kwargs["name"] = kwargs.get("name", type(self).__name__)
         super().__init__(**kwargs)
-        self.counters = dict(divergent=0, fix_zero=0, fix_other=0, fix_sec=0, other=0)
+        self.counters = {label: 0 for label in _CLASS_LABELS}
         self.interesting_fixpoints = []
 
     def run_net(self, net, step_limit=100, run_id=0):
-        """while i < step_limit and not diverged and not fixpoint: self_attack [; save_state(time=i)]; then count.
-        One fused launch when `net` is an engine net (always, unless a user subclass overrides the operator)."""
+        """Self-apply `net` until it diverges, becomes a fixpoint or `step_limit` is reached; log a state per step
+        when `run_id` is truthy; then classify it.  Engine nets do all of that in one fused launch."""
         fused = getattr(net, "_engine_run_until", None)
         if fused is not None and net._fused():
             fused(step_limit, log_states=bool(run_id))
-        else:
-            i = 0
-            while i < step_limit and not net.is_diverged() and not net.is_fixpoint():
+        else:                                   # user subclass with its own operator: the generic loop
+            steps_done = 0
+            while steps_done < step_limit and not net.is_diverged() and not net.is_fixpoint():
                 net.self_attack()
-                i += 1
+                steps_done += 1
                 if run_id:
-                    net.save_state(time=i)
+                    net.save_state(time=steps_done)
         self.count(net)
 
+    def _label_of(self, net):
+        fused = getattr(net, "_engine_class_name", None)
+        if fused is not None and net._fused():
+            return fused()
+        if net.is_diverged():
+            return "divergent"
+        if net.is_fixpoint():
+            return "fix_zero" if net.is_zero() else "fix_other"
+        return "fix_sec" if net.is_fixpoint(2) else "other"
+
     def count(self, net):
-        label = getattr(net, "_engine_class_name", None)
-        if label is not None and net._fused():
-            label = label()
-        elif net.is_diverged():
-            label = "divergent"
-        elif net.is_fixpoint():
-            label = "fix_zero" if net.is_zero() else "fix_other"
-        elif net.is_fixpoint(2):
-            label = "fix_sec"
-        else:
-            label = "other"
+        label = self._label_of(net)
         self.counters[label] += 1
         if label == "fix_other":
             self.interesting_fixpoints.append(net.get_weights())
@@ -117,26 +135,26 @@ class FixpointExperiment(Experiment):
 class MixedFixpointExperiment(FixpointExperiment):
 
     def run_net(self, net, trains_per_application=100, step_limit=100, run_id=0):
-        """Alternate one self_attack with `trains_per_application` train epochs (code/experiment.py:96-109)."""
-        i = 0
-        while i < step_limit and not net.is_diverged() and not net.is_fixpoint():
+        """Like run_net, but every self-application is followed by `trains_per_application` train() epochs
+        (code/experiment.py:96-109); the tqdm bar shows the running loss as the reference's does."""
+        rounds = 0
+        while rounds < step_limit and not net.is_diverged() and not net.is_fixpoint():
             net.self_attack()
             with tqdm(postfix=["Loss", dict(value=0)]) as bar:
                 for _ in range(trains_per_application):
-                    loss = net.compiled().train()
-                    bar.postfix[1]["value"] = loss
+                    bar.postfix[1]["value"] = net.compiled().train()
                     bar.update()
-            i += 1
+            rounds += 1
             if run_id:
                 net.save_state()
         self.count(net)
 
 
 class SoupExperiment(Experiment):
-    pass
+    """Plain Experiment; the reference uses the subclass name for the directory only."""
 
 
 class IdentLearningExperiment(Experiment):
 
     def __init__(self):
-        super(IdentLearningExperiment, self).__init__(name=self.__class__.__name__)
+        super().__init__(name=type(self).__name__)

@@ -1,34 +1,27 @@
-"""util -- host-side mirror of the reference's code/util.py (PrintingObject), the base class of every net.
+"""util -- host-side stand-in for the reference's code/util.py.
 
-Pure bookkeeping (a silence flag and a conditional print); nothing here touches the device.
+The reference's only utility is `PrintingObject`, the base class of every net: a verbosity switch plus a
+print that honours it.  Nothing here touches the device; it exists so that user code written against the
+reference (`net.silence()`, `net.with_silence(False)`, `net._print(...)`) keeps working.
 """
+import contextlib
 
 
 class PrintingObject:
-    """Same surface as code/util.py:1-39: is_silent/get_silence/set_silence/unset_silence/with_silence/
-    silence()/_print()."""
-
-    class SilenceSignal:
-        """Context manager returned by silence(): temporarily overrides the flag (code/util.py:3-12)."""
-
-        def __init__(self, obj, value):
-            self.obj, self.new_silent, self.old_silent = obj, value, None
-
-        def __enter__(self):
-            self.old_silent = self.obj.get_silence()
-            self.obj.set_silence(self.new_silent)
-
-        def __exit__(self, exception_type, exception_value, traceback):
-            self.obj.set_silence(self.old_silent)
+    """Verbosity switch shared by all nets.  Objects start silent, exactly like the reference's
+    (code/util.py:14-15); every setter returns `self` so calls can be chained."""
 
     def __init__(self):
         self.silent = True
 
+    # -- queries -------------------------------------------------------------------------------------
     def is_silent(self):
-        return self.silent
+        return bool(self.silent)
 
-    get_silence = is_silent
+    def get_silence(self):
+        return self.is_silent()
 
+    # -- setters (chainable) -------------------------------------------------------------------------
     def set_silence(self, value=True):
         self.silent = value
         return self
@@ -36,11 +29,32 @@ class PrintingObject:
     def unset_silence(self):
         return self.set_silence(False)
 
-    with_silence = set_silence
+    def with_silence(self, value=True):
+        return self.set_silence(value)
+
+    # -- scoped override -----------------------------------------------------------------------------
+    class SilenceSignal(contextlib.AbstractContextManager):
+        """`with net.silence(False): ...` -- the flag is switched for the block and put back afterwards,
+        also when the block raises."""
+
+        def __init__(self, obj, value):
+            self.obj, self.new_silent, self.old_silent = obj, value, obj.get_silence()
+
+        def __enter__(self):
+            self.old_silent = self.obj.get_silence()
+            self.obj.set_silence(self.new_silent)
+            return self
+
+        def __exit__(self, exc_type, exc, tb):
+            self.obj.set_silence(self.old_silent)
+            return False
 
     def silence(self, value=True):
-        return PrintingObject.SilenceSignal(self, value)
+        return type(self).SilenceSignal(self, value)
 
+    # -- output --------------------------------------------------------------------------------------
     def _print(self, *args, **kwargs):
-        if not self.silent:
-            print(*args, **kwargs)
+        """print(...) unless the object is silent."""
+        if self.is_silent():
+            return
+        print(*args, **kwargs)
