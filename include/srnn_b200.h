@@ -16,7 +16,10 @@
  *    NaN / Inf in the data is a domain state ("divergent"), never an error.
  *  - arithmetic: FP32, flush-to-zero, operation order and FMA placement pinned to the reference's
  *    committed Keras trajectories (DESIGN.md "Pinned arithmetic").
- *  - net shapes are compile-time instantiated (srnn_shape_supported()); others return SRNN_ERR_SHAPE.
+ *  - net shapes: the benchmarked ones are compile-time instantiated (fast path); every other shape with at most
+ *    SRNN_MAX_WEIGHTS weights runs the per-net operations (init, apply, forward, self_apply, classify, train) on
+ *    a generic run-time-shape path; srnn_kfv and srnn_soup_* exist for instantiated shapes only (SRNN_ERR_SHAPE).
+ *    srnn_shape_supported(): 1 = instantiated, 2 = generic path, 0 = invalid.
  */
 #ifndef SRNN_B200_H
 #define SRNN_B200_H

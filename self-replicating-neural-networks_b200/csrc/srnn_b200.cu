@@ -21,6 +21,7 @@
 
 #include "../../include/srnn_b200.h"
 #include "srnn_device.cuh"
+#include "srnn_generic.cuh"
 
 namespace srnn {
 
@@ -1116,8 +1117,20 @@ static inline long shape_key(int kind, int width, int depth, int aggs) {
 #define SRNN_DISPATCH(d)                                                                              \
     switch (shape_key((d)->kind, (d)->width, (d)->depth, (d)->aggregates)) {                          \
         SRNN_SHAPES(SRNN_CASE)                                                                        \
-        default: return fail(SRNN_ERR_SHAPE, "net shape not instantiated in libsrnn_b200 (see SRNN_SHAPES)%s"); \
+        default: return fail(SRNN_ERR_SHAPE, "this operation exists only for the net shapes instantiated in libsrnn_b200 (see SRNN_SHAPES)%s"); \
     }
+// same, but shapes outside SRNN_SHAPES run GENERIC (a statement using `dyn`, the run-time shape) instead of failing
+#define SRNN_DISPATCH_OR_GENERIC(d, ...)                                                              \
+    switch (shape_key((d)->kind, (d)->width, (d)->depth, (d)->aggregates)) {                          \
+        SRNN_SHAPES(SRNN_CASE)                                                                        \
+        default: {                                                                                    \
+            gen::DynShape dyn;                                                                        \
+            const int grc = gen::make_dyn(d, &dyn);                                                   \
+            if (grc) return fail(grc, "invalid or too large net shape%s");                            \
+            __VA_ARGS__                                                                               \
+        }                                                                                             \
+    }
+static inline unsigned ggrid(int64_t n) { return (unsigned)((n + gen::GBS - 1) / gen::GBS); }
 
 static inline unsigned grid_for(int64_t n) { return (unsigned)((n + BS - 1) / BS); }
 
@@ -1176,7 +1189,10 @@ int srnn_shape_supported(const srnn_net_desc *d) {
 #define BODY(S) return 1;
     switch (shape_key(d->kind, d->width, d->depth, d->aggregates)) {
         SRNN_SHAPES(SRNN_CASE)
-        default: return 0;
+        default: {
+            gen::DynShape dyn;
+            return gen::make_dyn(d, &dyn) == SRNN_OK ? 2 : 0;
+        }
     }
 #undef BODY
 }
@@ -1194,7 +1210,13 @@ int srnn_apply(const srnn_net_desc *d, const float *op_w, int64_t op_ld, const i
     SRNN_CHECK_ARENA(op_w, op_ld, S) SRNN_CHECK_ARENA(in_w, in_ld, S) SRNN_CHECK_ARENA(out_w, out_ld, S)     \
     apply_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(op_w, op_ld, op_idx, in_w, in_ld, in_idx, out_w, \
                                                                   out_ld, out_idx, n);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (!op_w || !in_w || !out_w) return fail(SRNN_ERR_ARG, "arena pointer is NULL%s");
+        if (op_ld < dyn.n_weights || in_ld < dyn.n_weights || out_ld < dyn.n_weights)
+            return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");
+        gen::apply_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(dyn, op_w, op_ld, op_idx, in_w, in_ld, in_idx, out_w,
+                                                                        out_ld, out_idx, n);
+    })
 #undef BODY
     return check_launch("srnn_apply");
 }
@@ -1206,7 +1228,13 @@ int srnn_forward(const srnn_net_desc *d, const float *w, int64_t ld, const int32
 #define BODY(S)                \
     SRNN_CHECK_ARENA(w, ld, S) \
     forward_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, idx, x, y, n);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (!w || ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "arena pointer is NULL or ld smaller than n_weights%s");
+        if (dyn.kind == SRNN_KIND_RNN)
+            gen::forward_rnn_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(dyn, w, ld, idx, x, y, n);
+        else
+            gen::forward_mlp_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(dyn, w, ld, idx, x, y, n);
+    })
 #undef BODY
     return check_launch("srnn_forward");
 }
@@ -1226,7 +1254,12 @@ int srnn_self_apply(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int
     if (fast) self_apply_fixed_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, n, n_steps);   \
     else self_apply_general_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(                         \
             w, ld, n, n_steps, mode, e, with_fix_sec, steps_out, cls_out, (unsigned long long *)counters, traj);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (!w || ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "arena pointer is NULL or ld smaller than n_weights%s");
+        if (fast) { int rc = make_eps(1e-14, &e); if (rc) return rc; }
+        gen::self_apply_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(
+            dyn, w, ld, n, n_steps, mode, e.ge, e.le, with_fix_sec, steps_out, cls_out, (unsigned long long *)counters, traj);
+    })
 #undef BODY
     return check_launch("srnn_self_apply");
 }
@@ -1242,7 +1275,11 @@ int srnn_classify(const srnn_net_desc *d, const float *w, int64_t ld, int64_t n,
     SRNN_CHECK_ARENA(w, ld, S)                                                                               \
     classify_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, n, e, with_fix_sec, cls_out, flags_out, \
                                                                      (unsigned long long *)counters);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (!w || ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "arena pointer is NULL or ld smaller than n_weights%s");
+        gen::classify_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(dyn, w, ld, n, e.ge, e.le, with_fix_sec, cls_out,
+                                                                           flags_out, (unsigned long long *)counters);
+    })
 #undef BODY
     return check_launch("srnn_classify");
 }
@@ -1263,7 +1300,14 @@ int srnn_train(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t 
     if (rc) return rc;                                                                                       \
     train_kernel<S><<<grid_for(n), BS, sm, (cudaStream_t)stream>>>(w, ld, n, n_epochs, lr, perm_mode, perm, seed, slot0, \
                                                                    epoch0, teacher_w, teacher_ld, teacher_idx, loss_out);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (!w || ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "arena pointer is NULL or ld smaller than n_weights%s");
+        if (teacher_w && teacher_ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "teacher_ld is smaller than n_weights%s");
+        if (dyn.kind == SRNN_KIND_RNN && dyn.n_layers * dyn.n_weights * dyn.hist_stride > gen::MAX_HIST)
+            return fail(SRNN_ERR_LIMIT, "recurrent net too large for the generic BPTT path%s");
+        gen::train_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(dyn, w, ld, n, n_epochs, lr, perm_mode, perm, seed, slot0,
+                                                                        epoch0, teacher_w, teacher_ld, teacher_idx, loss_out);
+    })
 #undef BODY
     return check_launch("srnn_train");
 }
@@ -1276,7 +1320,10 @@ int srnn_init(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, const int
 #define BODY(S)                \
     SRNN_CHECK_ARENA(w, ld, S) \
     init_kernel<S><<<grid_for(n), BS, 0, (cudaStream_t)stream>>>(w, ld, n, idx, seed, slot0, generation, lim);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (!w || ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "arena pointer is NULL or ld smaller than n_weights%s");
+        gen::init_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(dyn, w, ld, n, idx, seed, slot0, generation);
+    })
 #undef BODY
     return check_launch("srnn_init");
 }

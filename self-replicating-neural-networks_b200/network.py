@@ -172,9 +172,7 @@ class NeuralNetwork(PrintingObject):  # noqa: F405
 
     def _bind(self, kind, width, depth, aggregates=0):
         self._desc = _eng.make_desc(kind, width, depth, aggregates)
-        if not _eng.shape_supported(self._desc):
-            raise NotImplementedError("net shape (kind=%d, width=%d, depth=%d, aggregates=%d) is not instantiated in "
-                                      "libsrnn_b200; add it to SRNN_SHAPES in csrc/srnn_b200.cu" % (kind, width, depth, aggregates))
+        self._fast_shape = _eng.shape_supported(self._desc) == 1   # else: generic run-time-shape kernels (no soups)
         self._shapes = _eng.layer_shapes(self._desc)
         heap = _heap(self._desc)
         self._pop, token = heap.take()

@@ -72,7 +72,7 @@ class Soup(object):
         """Move the particles' records into one contiguous arena (row i = particles[i]) if they are engine nets of
         one shape; returns False when the soup is heterogeneous or uses user-overridden operators."""
         bases = [_base(p) for p in self.particles]
-        if not bases or any(b is None or not b._fused() for b in bases):
+        if not bases or any(b is None or not b._fused() or not b._fast_shape for b in bases):
             return False
         if len({b._desc.key() for b in bases}) != 1:
             return False

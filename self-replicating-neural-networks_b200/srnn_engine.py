@@ -79,7 +79,9 @@ def make_desc(kind, width=2, depth=2, aggregates=0):
 
 
 def shape_supported(d):
-    return bool(lib().srnn_shape_supported(C.byref(d)))
+    """0 = invalid shape, 1 = instantiated fast shape (every operation), 2 = generic run-time-shape path (the per-net
+    operations: init / apply / forward / self_apply / classify / train; no soups, no KFV sweep)."""
+    return int(lib().srnn_shape_supported(C.byref(d)))
 
 
 def layer_shapes(d):
@@ -143,8 +145,7 @@ class Population:
     def __init__(self, desc, n, device=None, ld=None, w=None):
         torch = _torch()
         if not shape_supported(desc):
-            raise SrnnError("net shape %r is not instantiated in libsrnn_b200 (SRNN_SHAPES in csrc/srnn_b200.cu)"
-                            % (desc.key(),))
+            raise SrnnError("net shape %r is not valid for libsrnn_b200" % (desc.key(),))
         self.desc = desc
         self.n = int(n)
         self.nw = int(desc.n_weights)

@@ -49,7 +49,8 @@ def test_bad_shapes_are_errors_not_crashes():
         eng.make_desc(0, 99, 2)
     with pytest.raises(eng.SrnnError):
         eng.make_desc(1, 1, 3, 4)          # 10 weights, 4 aggregates: leftovers (2) fill another collection
-    assert not eng.shape_supported(eng.make_desc(0, 4, 3))
+    assert eng.shape_supported(eng.make_desc(0, 4, 3)) == 2     # valid, served by the generic run-time-shape path
+    assert eng.shape_supported(eng.make_desc(0, 2, 2)) == 1
 
 
 def test_no_cpu_fallback():

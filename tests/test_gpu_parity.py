@@ -36,7 +36,7 @@ def test_descs_agree(eng):
         dg, do = both(eng, key)
         assert dg.n_weights == do.n_weights
         assert eng.shape_supported(dg)
-    assert not eng.shape_supported(eng.make_desc(0, 4, 3))
+    assert eng.shape_supported(eng.make_desc(0, 4, 3)) == 2
 
 
 # ---------------------------------------------------------------- K1 self-application
@@ -397,11 +397,16 @@ def test_empty_and_invalid_calls(eng):
                                C.c_int32(1), None, None, None, None, None) == 1
     assert lib.srnn_self_apply(C.byref(dg), p, C.c_int64(14), C.c_int64(4), C.c_int32(-1), C.c_int32(0), C.c_double(1e-4),
                                C.c_int32(1), None, None, None, None, None) == 1
-    # a shape that is valid but not instantiated
+    # a shape outside SRNN_SHAPES: per-net operations work (generic path), population-only operations refuse
     d2 = eng.make_desc(0, 4, 3)
     w2 = torch.zeros((4, d2.n_weights), dtype=torch.float32, device="cuda")
     assert lib.srnn_self_apply(C.byref(d2), C.c_void_p(w2.data_ptr()), C.c_int64(d2.n_weights), C.c_int64(4), C.c_int32(1),
-                               C.c_int32(0), C.c_double(1e-4), C.c_int32(1), None, None, None, None, None) == 2
+                               C.c_int32(0), C.c_double(1e-4), C.c_int32(1), None, None, None, None, None) == 0
+    base = np.zeros(d2.n_weights, np.float32)
+    assert lib.srnn_kfv(C.byref(d2), base.ctypes.data_as(C.c_void_p), C.c_int64(4), C.c_double(0.1), C.c_uint32(0),
+                        C.c_int32(10), C.c_double(1e-4), C.c_uint64(0), C.c_uint64(0), None, None, None, None,
+                        C.c_int64(d2.n_weights), None) == 2
+    assert b"SRNN_SHAPES" in lib.srnn_last_error_string()
     torch.cuda.synchronize()
     assert float(w.abs().sum()) == 0.0
 
@@ -421,4 +426,86 @@ def test_nan_inf_are_states_not_errors(eng):
     assert not np.isfinite(pop.numpy()[10:13]).all(axis=1).any()
     cls = pop.classify(1e-4)[0].cpu().numpy()
     assert (cls[[0, 1, 2, 10, 11, 12]] == 0).all()
+
+
+# ---------------------------------------------------------------- generic run-time-shape path
+GENERIC_SHAPES = [(0, 4, 3, 0), (0, 1, 1, 0), (0, 5, 2, 0), (1, 3, 3, 5), (1, 4, 1, 2), (2, 3, 2, 0), (2, 1, 3, 0)]
+
+
+@pytest.mark.parametrize("key", GENERIC_SHAPES)
+def test_generic_shapes_bitwise(eng, key):
+    """Shapes outside SRNN_SHAPES take the run-time-shape kernels: init, self_apply (fixed / run_net / trajectory /
+    classes), classify + flags, attack pairs, forward, train and learn_from -- all bit-for-bit equal to the oracle."""
+    dg, do = both(eng, key)
+    assert eng.shape_supported(dg) == 2
+    n = 600
+    pop = eng.Population(dg, n).init(seed=8, slot0=3, generation=2)
+    ref = np.zeros((n, do.n_weights), np.float32)
+    oracle.init(do, ref, seed=8, slot0=3, generation=2)
+    assert_same_weights(pop.numpy(), ref, "init")
+    w = glorot_population(key, n, seed=14)
+    pop = eng.Population.from_numpy(dg, w)
+    pop.self_apply(6)
+    ref = w.copy()
+    oracle.self_apply(do, ref, 6)
+    assert_same_weights(pop.numpy(), ref, "self_apply fixed")
+    pop = eng.Population.from_numpy(dg, w)
+    out = pop.self_apply(50, mode=eng.RUN_UNTIL, eps=1e-4, want_steps=True, want_cls=True, want_counters=True, want_traj=True)
+    ref = w.copy()
+    steps, traj = oracle.self_apply(do, ref, 50, mode=oracle.RUN_UNTIL, eps=1e-4, traj=True)
+    cls, cnt = oracle.classify(do, ref, 1e-4)
+    assert np.array_equal(out["steps"].cpu().numpy(), steps) and np.array_equal(out["cls"].cpu().numpy(), cls)
+    assert out["counters"].cpu().numpy().tolist() == cnt.tolist()
+    assert_same_weights(pop.numpy(), ref, "run_net")
+    gt = out["traj"].cpu().numpy()
+    for i in range(0, n, 53):
+        assert_same_weights(gt[:steps[i], i], traj[:steps[i], i])
+    c2, n2, flags = pop.classify(1e-4, want_flags=True)
+    assert np.array_equal(c2.cpu().numpy(), cls) and np.array_equal(flags.cpu().numpy(), oracle.predicates(do, ref, 1e-4))
+    # attack pairs
+    pop = eng.Population.from_numpy(dg, w)
+    att, vic = np.arange(0, n // 2), np.arange(n // 2, n)
+    pop.attack(att, vic)
+    ref = w.copy()
+    oracle.apply(do, ref, att, ref, vic, ref, vic, n // 2)
+    assert_same_weights(pop.numpy(), ref, "attack")
+    # forward
+    io = 4 if key[0] == 0 else (key[3] if key[0] == 1 else dg.n_weights)
+    x = np.random.default_rng(1).uniform(-1, 1, (n, io)).astype(np.float32)
+    assert_same_weights(eng.Population.from_numpy(dg, w).forward(x).cpu().numpy(), oracle.forward(do, w, x), "forward")
+    # train / learn_from
+    for pm in (0, 2):
+        pop = eng.Population.from_numpy(dg, w)
+        loss = pop.train(4, perm_mode=pm, seed=5, slot0=7, epoch0=1)
+        ref = w.copy()
+        rl = oracle.train(do, ref, 4, perm_mode=pm, seed=5, slot0=7, epoch0=1)
+        assert_same_weights(pop.numpy(), ref, "train perm %d" % pm)
+        gl = loss.cpu().numpy()
+        assert np.array_equal(np.isnan(gl), np.isnan(rl)) and np.array_equal(gl[~np.isnan(gl)], rl[~np.isnan(rl)])
+    t = glorot_population(key, n, seed=15)
+    pop, tea = eng.Population.from_numpy(dg, w), eng.Population.from_numpy(dg, t)
+    pop.train(3, perm_mode=2, seed=9, teacher=tea, teacher_idx=np.arange(n)[::-1].copy())
+    ref = w.copy()
+    oracle.train(do, ref, 3, perm_mode=2, seed=9, teacher_w=t, teacher_idx=np.arange(n)[::-1].copy())
+    assert_same_weights(pop.numpy(), ref, "learn_from")
+
+
+def test_generic_shape_facade(eng):
+    """The class API accepts any shape: a WeightwiseNeuralNetwork(width=3, depth=3) self-attacks, trains and sits in a
+    Soup (object-wise evolve, since soups' fused kernels exist for the instantiated shapes only)."""
+    import network
+    import soup as soup_mod
+    net = network.TrainingNeuralNetworkDecorator(network.ParticleDecorator(network.WeightwiseNeuralNetwork(3, 3)))
+    w0 = net.get_weights_flat()
+    do = oracle.desc(0, 3, 3, 0)
+    net.self_attack(2)
+    ref = w0[None].copy()
+    oracle.self_apply(do, ref, 2)
+    assert_same_weights(net.get_weights_flat(), ref[0])
+    assert isinstance(net.train(store_states=False), float)
+    s = soup_mod.Soup(6, lambda: network.TrainingNeuralNetworkDecorator(network.WeightwiseNeuralNetwork(3, 3))
+                      .with_params(epsilon=1e-4)).with_params(train=1, remove_divergent=True, remove_zero=True)
+    s.seed()
+    s.evolve(3)
+    assert sum(s.count().values()) == 6 and s.time == 3
 
