@@ -211,14 +211,33 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
         out["soup"] = {"metric": "soup generations/sec", "value": 1000 / dt, "unit": "generations/s",
                        "config": dict(workload="soup_100k_ww", particles=100_000, generations=1000, mode="snapshot-synchronous", **kw),
                        "particle_generations_per_s": 100_000 * 1000 / dt, "classes_after": s.count()}
+        # the same soup with the reference's exact sequential semantics (dependency-levelled wavefront, bit-identical
+        # to Soup.evolve's particle-by-particle sweep)
+        s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, order="exact", **kw).seed_particles()
+        s.evolve(10)
+        dt = _timed(torch, lambda: s.evolve(200))
+        out["soup_exact_order"] = {"metric": "soup generations/sec", "value": 200 / dt, "unit": "generations/s",
+                                   "config": dict(workload="soup_100k_ww_exact_order", particles=100_000, generations=200,
+                                                  mode="exact sequential order (wavefront)", **kw),
+                                   "rounds_last_generation": s.rounds, "classes_after": s.count()}
         # same soup at 10M particles, train=0 (configs[3]'s per-GPU regime): one HBM pass per generation
         kw0 = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, remove_divergent=True, remove_zero=True, epsilon=1e-4)
         s = PopulationSoup(eng.KIND_WW, 10_000_000, seed=4, **kw0).seed_particles()
         s.evolve(4)
         dt = _timed(torch, lambda: s.evolve(20))
+        hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        try:
+            hbm_peak, peak_src = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json"
+        except Exception:
+            pass
+        ach = 10_000_000 * 130.0 * 20 / dt / 1e9
         out["soup_10m"] = {"metric": "soup generations/sec", "value": 20 / dt, "unit": "generations/s",
                            "config": dict(workload="soup_10m_ww_train0", particles=10_000_000, generations=20, **kw0),
-                           "hbm_gbs_algorithmic": 10_000_000 * 130.0 * 20 / dt / 1e9}
+                           "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                                        "traffic": 1.645e9, "peak_source": peak_src, "kernel": "soup_sync_kernel<WW(2,2)>",
+                                        "algorithmic_bytes": "130 B per particle-generation (112 B own record in/out + 0.2 x 56 B "
+                                                             "partner records + list heads)",
+                                        "traffic_source": "ncu dram bytes of one launch at 10 M particles (1.05 GB read + 0.59 GB write)"}}
         del s
         # configs[1]: self-training, 10k WW + 10k AGG(4) x 1000 epochs; and a 2^20-net WW run for throughput
         dw, da = eng.make_desc(eng.KIND_WW, 2, 2), eng.make_desc(eng.KIND_AGG, 2, 2, 4)

@@ -117,6 +117,19 @@ int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *
                       double *loss, float *logged, const float *spares, int64_t spare_ld, int32_t n_spares,
                       int32_t *spares_used, void *stream);
 
+/* Soup.evolve (code/soup.py:51-87) with the reference's EXACT sequential semantics at population scale: the result is
+ * bit-identical to visiting the particles one by one in index order (= srnn_soup_ordered), but the generation runs
+ * as a dependency-levelled wavefront of parallel rounds, in place on `w` (DESIGN.md "Soup modes").
+ *   att / lrn  int64[n] device arrays of target indices or -1 (host-drawn, e.g. Python `random` in the reference's
+ *              order); both NULL = Philox draws of (seed, particle, gen), the same function srnn_soup_sync uses
+ *   scratch    int32[7*n + 16], no initialisation needed
+ *   action uint8[n], loss double[n], dead uint8[n] (all nullable); *rounds_out (HOST int, nullable) = rounds used
+ * Respawn = srnn_init(seed, slot, gen).  Unsharded soups only.  The call synchronises the stream once per round
+ * (it reads the progress counter back), so unlike the other entry points it returns after the work is done. */
+int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, const int64_t *att,
+                    const int64_t *lrn, uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss,
+                    uint8_t *dead, int32_t *rounds_out, void *stream);
+
 /* Soup.evolve, snapshot-synchronous generation for large / sharded soups (DESIGN.md "Soup modes"): every
  * partner is read from `snap`, the start-of-generation arena of ALL n_total particles (after the
  * per-generation all-gather when sharded); this call owns particles [slot0, slot0+n) and writes their

@@ -566,6 +566,107 @@ __global__ void soup_ordered_kernel(float *w, int64_t ld, int64_t n, const int64
     if (spares_used_out) *spares_used_out = used;
 }
 
+// ---------------------------------------------------------------------------------------------- exact order at scale
+// Soup.evolve's sequential semantics (particle i sees every write of particles < i) WITHOUT serialising the soup: a
+// dependency-levelled wavefront.  Event j (particle j's turn) touches particle j, its victim a_j and its teacher l_j.
+// For every particle the events touching it -- its own turn, its attackers, its learners -- form a chain ordered by
+// event index; event j may run as soon as its immediate predecessor in each of its (up to three) chains has run.
+// Events that become ready in the same round cannot share a particle (the earlier one would be an unfinished
+// predecessor of the later one), so a round is one fully parallel kernel working in place on the arena; the number
+// of rounds is the depth of the dependency DAG (a few tens for random pairings).
+__global__ void __launch_bounds__(BS) soup_exact_lists_kernel(SoupP p, uint64_t seed, uint64_t gen, int64_t n,
+                                                              const int64_t *__restrict__ att_in,
+                                                              const int64_t *__restrict__ lrn_in, int32_t *att32,
+                                                              int32_t *lrn32, int32_t *headA, int32_t *nextA,
+                                                              int32_t *headL, int32_t *nextL) {
+    const int64_t i = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (i >= n) return;
+    int64_t a, l;
+    if (att_in) {
+        a = att_in[i];
+        l = lrn_in ? lrn_in[i] : -1;
+    } else {
+        soup_draw(p, seed, (uint64_t)i, gen, n, &a, &l);
+    }
+    att32[i] = (int32_t)a;
+    lrn32[i] = (int32_t)l;
+    if (a >= 0) nextA[i] = atomicExch(&headA[a], (int32_t)i);
+    if (l >= 0) nextL[i] = atomicExch(&headL[l], (int32_t)i);
+}
+
+// the latest event before j that touches particle p (its own turn, an attack on it, a learn_from it), or -1
+__device__ __forceinline__ int32_t chain_pred(int32_t p, int32_t j, const int32_t *__restrict__ headA,
+                                              const int32_t *__restrict__ nextA, const int32_t *__restrict__ headL,
+                                              const int32_t *__restrict__ nextL) {
+    int32_t best = p < j ? p : -1;
+    for (int32_t e = headA[p]; e >= 0; e = nextA[e])
+        if (e < j && e > best) best = e;
+    for (int32_t e = headL[p]; e >= 0; e = nextL[e])
+        if (e < j && e > best) best = e;
+    return best;
+}
+
+template <class S>
+__global__ void __launch_bounds__(BS) soup_exact_round_kernel(float *w, int64_t ld, int64_t n, SoupP p, uint64_t seed,
+                                                              uint64_t gen, Limits lim, const int32_t *__restrict__ att32,
+                                                              const int32_t *__restrict__ lrn32,
+                                                              const int32_t *__restrict__ headA,
+                                                              const int32_t *__restrict__ nextA,
+                                                              const int32_t *__restrict__ headL,
+                                                              const int32_t *__restrict__ nextL,
+                                                              const uint8_t *__restrict__ done_prev, uint8_t *done_cur,
+                                                              uint8_t *action, double *loss, uint8_t *dead_out,
+                                                              unsigned long long *n_done) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    SgdScratch sc = sgd_scratch<S>(smem, BS);
+    __syncthreads();  // position codes visible
+    const int64_t j64 = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (j64 >= n) return;
+    const int32_t j = (int32_t)j64;
+    if (done_prev[j]) { done_cur[j] = 1; return; }
+    const int32_t a = att32[j], l = lrn32[j];
+    int32_t pr = chain_pred(j, j, headA, nextA, headL, nextL);
+    bool ready = pr < 0 || done_prev[pr];
+    if (ready && a >= 0 && a != j) { pr = chain_pred(a, j, headA, nextA, headL, nextL); ready = pr < 0 || done_prev[pr]; }
+    if (ready && l >= 0 && l != j && l != a) { pr = chain_pred(l, j, headA, nextA, headL, nextL); ready = pr < 0 || done_prev[pr]; }
+    if (!ready) { done_cur[j] = 0; return; }
+    // ---- particle j's turn, exactly as code/soup.py:55-87 (same body as the single-thread ordered kernel)
+    float cur[S::NW], oth[S::NW], res[S::NW];
+    uint8_t act = SRNN_ACT_NONE;
+    double ls = nan("");
+    bool dead = false;
+    {
+        const float *rec = w + j64 * ld;
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) cur[k] = rec[k];
+    }
+    if (a >= 0) {
+        const float *vr = w + (int64_t)a * ld;
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) oth[k] = vr[k];
+        net_apply<S>(cur, oth, res, sc.one);
+        record_store<S::NW>(w, ld, a, res);
+        if (a == j) {
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
+        }
+        act = SRNN_ACT_ATTACK;
+    }
+    const bool has_teacher = l >= 0 && l != j, self_teacher = l == j;
+    if (has_teacher) {
+        const float *tr = w + (int64_t)l * ld;   // plain load: the teacher may have been rewritten in an earlier round
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tr[k];
+    }
+    soup_tail<S>(p, cur, sc, has_teacher, self_teacher, seed, (uint64_t)j, gen, lim, &act, &ls, nullptr, 0, 0, &dead);
+    record_store<S::NW>(w, ld, j64, cur);
+    if (action) action[j] = act;
+    if (loss) loss[j] = ls;
+    if (dead_out) dead_out[j] = dead ? 1 : 0;
+    done_cur[j] = 1;
+    atomicAdd(n_done, 1ull);
+}
+
 // snapshot-synchronous, phase A: every owner evaluates the same pairing function for ALL global particles and
 // threads the attackers of its local victims into per-victim lists (head[n] | next[n_total]).
 __global__ void __launch_bounds__(BS) soup_lists_kernel(SoupP p, uint64_t seed, uint64_t gen, int64_t n_total,
@@ -1458,6 +1559,52 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
     tab.n = n_shards;
     return soup_sync_impl(d, p, tab, shards[my_shard], ld, shard_len * n_shards, w_out, out_ld, (int64_t)my_shard * shard_len,
                           shard_len, seed, gen, scratch, action, loss, dead, stream);
+}
+
+int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, const int64_t *att,
+                    const int64_t *lrn, uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss,
+                    uint8_t *dead, int32_t *rounds_out, void *stream) {
+    if (!d || !scratch) return fail(SRNN_ERR_ARG, "desc or scratch is NULL%s");
+    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    if (n >= 0x7fffffffLL) return fail(SRNN_ERR_ARG, "need n < 2^31%s");
+    SoupP q;
+    int rc = make_soup(p, &q);
+    if (rc) return rc;
+    const Limits lim = make_limits(d);
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t *headA = scratch, *nextA = headA + n, *headL = nextA + n, *nextL = headL + n, *att32 = nextL + n,
+            *lrn32 = att32 + n;
+    uint8_t *done0 = reinterpret_cast<uint8_t *>(lrn32 + n), *done1 = done0 + n;
+    unsigned long long *n_done = reinterpret_cast<unsigned long long *>(scratch + 6 * n + (2 * n + 3) / 4 + 2);
+    n_done = reinterpret_cast<unsigned long long *>((reinterpret_cast<uintptr_t>(n_done) + 7) & ~uintptr_t(7));
+    cudaError_t ce = cudaMemsetAsync(headA, 0xFF, sizeof(int32_t) * (size_t)n, st);
+    if (ce == cudaSuccess) ce = cudaMemsetAsync(headL, 0xFF, sizeof(int32_t) * (size_t)n, st);
+    if (ce == cudaSuccess) ce = cudaMemsetAsync(done0, 0, (size_t)n, st);
+    if (ce == cudaSuccess) ce = cudaMemsetAsync(n_done, 0, sizeof(unsigned long long), st);
+    if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    soup_exact_lists_kernel<<<grid_for(n), BS, 0, st>>>(q, seed, gen, n, att, lrn, att32, lrn32, headA, nextA, headL, nextL);
+    int rounds = 0;
+    unsigned long long done_host = 0;
+    while (done_host < (unsigned long long)n) {
+        if (rounds >= 1 << 16) return fail(SRNN_ERR_LIMIT, "srnn_soup_exact: dependency chain deeper than 65536 rounds%s");
+        const uint8_t *dp = (rounds & 1) ? done1 : done0;
+        uint8_t *dc = (rounds & 1) ? done0 : done1;
+#define BODY(S)                                                                                              \
+    SRNN_CHECK_ARENA(w, ld, S)                                                                               \
+    const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
+    rc = allow_smem(soup_exact_round_kernel<S>, sm);                                                         \
+    if (rc) return rc;                                                                                       \
+    soup_exact_round_kernel<S><<<grid_for(n), BS, sm, st>>>(w, ld, n, q, seed, gen, lim, att32, lrn32, headA, nextA, headL, \
+                                                            nextL, dp, dc, action, loss, dead, n_done);
+        SRNN_DISPATCH(d)
+#undef BODY
+        ++rounds;
+        ce = cudaMemcpyAsync(&done_host, n_done, sizeof done_host, cudaMemcpyDeviceToHost, st);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+        if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "srnn_soup_exact: %s", cudaGetErrorString(ce));
+    }
+    if (rounds_out) *rounds_out = rounds;
+    return SRNN_OK;
 }
 
 int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w_a, float *w_b, int64_t ld, int64_t n,

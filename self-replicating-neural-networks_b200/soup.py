@@ -256,6 +256,9 @@ class _CudaBackend:
             warnings.warn("PopulationSoup: peer memory unavailable (%s); using the all-gather exchange" % (exc,))
             return None
 
+    def soup_exact(self, desc, sp_kwargs, w, seed, gen, scratch, action, dead):
+        return _eng.soup_exact(desc, _eng.make_soup_params(**sp_kwargs), w, seed, gen, scratch, action=action, dead=dead)
+
     def soup_sync_run(self, desc, sp_kwargs, w_a, w_b, seed, gen0, n_gens, scratch, action, dead):
         _eng.soup_sync_run(desc, _eng.make_soup_params(**sp_kwargs), w_a, w_b, seed, gen0, n_gens, scratch,
                            action=action, dead=dead)
@@ -289,7 +292,7 @@ class PopulationSoup:
     so the result does not depend on how the population is sharded."""
 
     def __init__(self, kind, size, width=2, depth=2, aggregates=0, seed=0, group=None, device=None, backend=None,
-                 exchange="auto", **params):
+                 exchange="auto", order="snapshot", **params):
         import torch
         import torch.distributed as dist
         self.desc = _eng.make_desc(kind, width, depth, aggregates)
@@ -303,6 +306,13 @@ class PopulationSoup:
                            remove_divergent=False, remove_zero=False, epsilon=1e-4, perm_mode=_eng.PERM_PHILOX,
                            engine_path=0)
         self.params.update(params)
+        # order="snapshot": partners read from the start-of-generation arena (default, shards over GPUs);
+        # order="exact": the reference's sequential sweep, bit for bit, as a parallel wavefront (unsharded soups)
+        if order not in ("snapshot", "exact"):
+            raise ValueError("order must be 'snapshot' or 'exact'")
+        if order == "exact" and self.world > 1:
+            raise ValueError("exact-order generations are implemented for unsharded soups")
+        self.order, self.rounds = order, 0
         self.backend = backend or _CudaBackend(device)
         nw, B = self.desc.n_weights, self.backend
         # exchange of a sharded soup: "peer" = partner records are read straight from the owning GPU's arena over
@@ -322,7 +332,7 @@ class PopulationSoup:
             self.w = B.alloc((self.n_local, nw), torch.float32)
             self._next = B.alloc((self.n_local, nw), torch.float32)
             self._snap = B.alloc((self.size, nw), torch.float32) if self.world > 1 else None
-        self._scratch = B.alloc((_eng.soup_scratch_len(self.size, self.n_local),), torch.int32)
+        self._scratch = B.alloc((max(_eng.soup_scratch_len(self.size, self.n_local), 7 * self.size + 16),), torch.int32)
         self.dead = B.alloc((self.n_local,), torch.uint8)
         self.action = B.alloc((self.n_local,), torch.uint8)
         self.uid = B.alloc((self.n_local,), torch.int64)
@@ -355,6 +365,13 @@ class PopulationSoup:
     def evolve(self, iterations=1):
         import torch.distributed as dist
         sp, B = self._sp(), self.backend
+        if self.order == "exact":
+            for _ in range(iterations):
+                self.time += 1
+                self.rounds = B.soup_exact(self.desc, sp, self.w, self.seed, self.time, self._scratch, self.action, self.dead)
+                if self.track_uids:
+                    self._assign_uids()
+            return self
         if self.world == 1 and not self.track_uids and iterations > 1 and hasattr(B, "soup_sync_run"):
             # unsharded: all generations in one C call (no per-generation host overhead)
             B.soup_sync_run(self.desc, sp, self.w, self._next, self.seed, self.time + 1, iterations, self._scratch,

@@ -28,7 +28,7 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
 UIDS_STATIC_MAX = 1 << 24
 
 
@@ -284,6 +284,16 @@ def soup_sync(desc, params, snap, n_total, w_out, slot0, n, seed, gen, scratch, 
     _chk(lib().srnn_soup_sync(C.byref(desc), C.byref(params), _ptr(snap), C.c_int64(snap.shape[1]), C.c_int64(n_total),
                               _ptr(w_out), C.c_int64(w_out.shape[1]), C.c_int64(slot0), C.c_int64(n), C.c_uint64(seed),
                               C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead), _stream()))
+
+
+def soup_exact(desc, params, w, seed, gen, scratch, att=None, lrn=None, action=None, loss=None, dead=None):
+    """One generation with the reference's exact sequential semantics, run as a parallel wavefront (in place on w).
+    att / lrn: int64 device tensors of targets (or None for Philox draws).  Returns the number of rounds."""
+    rounds = C.c_int32(0)
+    _chk(lib().srnn_soup_exact(C.byref(desc), C.byref(params), _ptr(w), C.c_int64(w.shape[1]), C.c_int64(w.shape[0]),
+                               _ptr(att), _ptr(lrn), C.c_uint64(seed), C.c_uint64(gen), _ptr(scratch), _ptr(action),
+                               _ptr(loss), _ptr(dead), C.byref(rounds), _stream()))
+    return rounds.value
 
 
 def soup_sync_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action=None, loss=None,

@@ -509,3 +509,56 @@ def test_generic_shape_facade(eng):
     s.evolve(3)
     assert sum(s.count().values()) == 6 and s.time == 3
 
+
+# ---------------------------------------------------------------- exact-order generations at scale
+@pytest.mark.parametrize("key", BENCH_SHAPES)
+def test_soup_exact_order_wavefront(eng, key):
+    """srnn_soup_exact == the sequential sweep of Soup.evolve (oracle soup_ordered), bit for bit, on 20k particles:
+    Philox-drawn pairings (the function the oracle's soup_draw evaluates) and host-supplied pairings."""
+    import torch
+    dg, do = both(eng, key)
+    n = 20000
+    kw = dict(attacking_rate=0.3, learn_from_rate=0.2, train=1, learn_from_severity=2, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population(key, n, seed=61)
+    arena = torch.from_numpy(w).cuda()
+    ref = w.copy()
+    scratch = torch.zeros(7 * n + 16, dtype=torch.int32, device="cuda")
+    action = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    loss = torch.zeros(n, dtype=torch.float64, device="cuda")
+    rng = np.random.default_rng(3)
+    for gen in range(1, 4):
+        if gen < 3:      # device draws
+            att, lrn = oracle.soup_draw(po, 29, gen, n)
+            rounds = eng.soup_exact(dg, pg, arena, 29, gen, scratch, action=action, loss=loss)
+        else:            # host-supplied pairings, including self-attacks and self-teaching
+            att = np.where(rng.random(n) < 0.3, rng.integers(0, n, n), -1)
+            lrn = np.where(rng.random(n) < 0.2, rng.integers(0, n, n), -1)
+            att[:50] = np.arange(50)
+            lrn[50:100] = np.arange(50, 100)
+            rounds = eng.soup_exact(dg, pg, arena, 29, gen, scratch, att=torch.from_numpy(att).cuda(),
+                                    lrn=torch.from_numpy(lrn).cuda(), action=action, loss=loss)
+        ra, rl = oracle.soup_ordered(do, po, ref, att, lrn, seed=29, gen=gen)
+        assert 2 <= rounds < 200
+        assert_same_weights(arena.cpu().numpy(), ref, "generation %d (%d rounds)" % (gen, rounds))
+        assert np.array_equal(action.cpu().numpy(), ra)
+        gl = loss.cpu().numpy()
+        assert np.array_equal(np.isnan(gl), np.isnan(rl)) and np.array_equal(gl[~np.isnan(gl)], rl[~np.isnan(rl)])
+
+
+def test_population_soup_exact_mode(eng):
+    import soup as soup_mod
+    n = 6000
+    kw = dict(seed=13, attacking_rate=0.2, learn_from_rate=0.2, train=1, remove_divergent=True, remove_zero=True)
+    s = soup_mod.PopulationSoup(eng.KIND_WW, n, order="exact", **kw).seed_particles()
+    ref = s.local.numpy().copy()
+    po = oracle.soup_params(attacking_rate=0.2, learn_from_rate=0.2, train=1, learn_from_severity=1, remove_divergent=True,
+                            remove_zero=True, epsilon=1e-4, perm_mode=2)
+    for gen in range(1, 4):
+        s.evolve()
+        att, lrn = oracle.soup_draw(po, 13, gen, n)
+        oracle.soup_ordered(oracle.ww(), po, ref, att, lrn, seed=13, gen=gen)
+        assert_same_weights(s.local.numpy(), ref, "generation %d" % gen)
+    assert s.rounds >= 2 and sum(s.count().values()) == n
+
