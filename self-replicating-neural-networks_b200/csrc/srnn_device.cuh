@@ -117,11 +117,14 @@ SRNN_DEV f32x2_t fma2(f32x2_t a, f32x2_t b, f32x2_t c) {
 template <int IN, int OUT>
 SRNN_DEV void dense(const float *x, const float *W, float *y) {
 #if SRNN_PACKED_F32X2
-    if constexpr (OUT == 2) {  // R2, both units at once: acc = rn(x0*W0j); acc = fma(xk, Wkj, acc)
-        f32x2_t acc = mul2(pack2(x[0], x[0]), pack2(W[0], W[1]));
+    if constexpr (OUT % 2 == 0) {  // R2, two units per instruction: acc = rn(x0*W0j); acc = fma(xk, Wkj, acc)
 #pragma unroll
-        for (int k = 1; k < IN; ++k) acc = fma2(pack2(x[k], x[k]), pack2(W[2 * k], W[2 * k + 1]), acc);
-        unpack2(acc, y[0], y[1]);
+        for (int j = 0; j < OUT; j += 2) {
+            f32x2_t acc = mul2(pack2(x[0], x[0]), pack2(W[j], W[j + 1]));
+#pragma unroll
+            for (int k = 1; k < IN; ++k) acc = fma2(pack2(x[k], x[k]), pack2(W[k * OUT + j], W[k * OUT + j + 1]), acc);
+            unpack2(acc, y[j], y[j + 1]);
+        }
         return;
     } else if constexpr (OUT == 1 && IN == 2) {  // R3: the two products in one instruction, adds unfused from +0
         float p0, p1;
@@ -418,12 +421,16 @@ SRNN_DEV float mlp_sgd_sample(float *w, const float *x, const float *y, float lr
 #if SRNN_PACKED_F32X2
         // W <- rn(W - rn(lr * rn(act*g))) two weights at a time.  The subtraction is spelled fma(1, -step, W) with the
         // run-time 1 (opaque_one) so that ptxas cannot contract it with the multiply before it.
-        if constexpr (OUT == 2) {
-            const f32x2_t gpair = pack2(g[0], g[1]), nlr = pack2(-lr, -lr), ones = pack2(one, one);
+        if constexpr (OUT % 2 == 0) {
+            const f32x2_t nlr = pack2(-lr, -lr), ones = pack2(one, one);
 #pragma unroll
-            for (int i = 0; i < IN; ++i) {
-                const f32x2_t step = mul2(nlr, mul2(pack2(act[l][i], act[l][i]), gpair));
-                unpack2(fma2(ones, step, pack2(W[2 * i], W[2 * i + 1])), W[2 * i], W[2 * i + 1]);
+            for (int j = 0; j < OUT; j += 2) {
+                const f32x2_t gpair = pack2(g[j], g[j + 1]);
+#pragma unroll
+                for (int i = 0; i < IN; ++i) {
+                    const f32x2_t step = mul2(nlr, mul2(pack2(act[l][i], act[l][i]), gpair));
+                    unpack2(fma2(ones, step, pack2(W[i * OUT + j], W[i * OUT + j + 1])), W[i * OUT + j], W[i * OUT + j + 1]);
+                }
             }
         } else if constexpr (OUT == 1 && IN == 2) {
             const f32x2_t step = mul2(pack2(-lr, -lr), mul2(pack2(act[l][0], act[l][1]), pack2(g[0], g[0])));
