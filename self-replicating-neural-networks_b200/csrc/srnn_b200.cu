@@ -2,7 +2,7 @@
 //
 // Build (see __graft_entry__.build):
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -ftz=true
-//        -prec-div=true -prec-sqrt=true -Xcompiler -fPIC -shared -o libsrnn_b200.so srnn_b200.cu
+//        -prec-div=true -prec-sqrt=true -Xcompiler -fPIC -shared --split-compile 0 -o libsrnn_b200.so srnn_b200.cu
 //
 // Execution model: one thread owns one net.  A CTA of 256 threads stages its tile of 256 contiguous
 // records (256 * n_weights floats) between HBM and shared memory with fully coalesced accesses, then
