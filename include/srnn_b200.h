@@ -123,9 +123,9 @@ int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *
  *   att / lrn  int64[n] device arrays of target indices or -1 (host-drawn, e.g. Python `random` in the reference's
  *              order); both NULL = Philox draws of (seed, particle, gen), the same function srnn_soup_sync uses
  *   scratch    int32[7*n + 16], no initialisation needed
- *   action uint8[n], loss double[n], dead uint8[n] (all nullable); *rounds_out (HOST int, nullable) = rounds used
- * Respawn = srnn_init(seed, slot, gen).  Unsharded soups only.  The call synchronises the stream once per round
- * (it reads the progress counter back), so unlike the other entry points it returns after the work is done. */
+ *   action uint8[n], loss double[n], dead uint8[n] (all nullable); *rounds_out (HOST int, nullable) = rounds launched (a multiple of 4 >= the DAG depth)
+ * Respawn = srnn_init(seed, slot, gen).  Unsharded soups only.  The call synchronises the stream once per batch of
+ * 4 rounds (it reads the progress counter back), so unlike the other entry points it returns after the work is done. */
 int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, const int64_t *att,
                     const int64_t *lrn, uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss,
                     uint8_t *dead, int32_t *rounds_out, void *stream);

@@ -1585,10 +1585,14 @@ int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w,
     soup_exact_lists_kernel<<<grid_for(n), BS, 0, st>>>(q, seed, gen, n, att, lrn, att32, lrn32, headA, nextA, headL, nextL);
     int rounds = 0;
     unsigned long long done_host = 0;
+    // Rounds are launched in batches before the progress counter is read back (one host synchronisation per batch
+    // instead of per round); a round after completion only copies done flags, so overshooting is cheap.
+    const int batch = 4;
     while (done_host < (unsigned long long)n) {
         if (rounds >= 1 << 16) return fail(SRNN_ERR_LIMIT, "srnn_soup_exact: dependency chain deeper than 65536 rounds%s");
-        const uint8_t *dp = (rounds & 1) ? done1 : done0;
-        uint8_t *dc = (rounds & 1) ? done0 : done1;
+        for (int b = 0; b < batch; ++b, ++rounds) {
+            const uint8_t *dp = (rounds & 1) ? done1 : done0;
+            uint8_t *dc = (rounds & 1) ? done0 : done1;
 #define BODY(S)                                                                                              \
     SRNN_CHECK_ARENA(w, ld, S)                                                                               \
     const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
@@ -1596,9 +1600,9 @@ int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w,
     if (rc) return rc;                                                                                       \
     soup_exact_round_kernel<S><<<grid_for(n), BS, sm, st>>>(w, ld, n, q, seed, gen, lim, att32, lrn32, headA, nextA, headL, \
                                                             nextL, dp, dc, action, loss, dead, n_done);
-        SRNN_DISPATCH(d)
+            SRNN_DISPATCH(d)
 #undef BODY
-        ++rounds;
+        }
         ce = cudaMemcpyAsync(&done_host, n_done, sizeof done_host, cudaMemcpyDeviceToHost, st);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
         if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "srnn_soup_exact: %s", cudaGetErrorString(ce));
