@@ -239,6 +239,30 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
                                                              "partner records + list heads)",
                                         "traffic_source": "ncu dram bytes of one launch at 10 M particles (1.05 GB read + 0.59 GB write)"}}
         del s
+        # configs[4]: known-fixpoint variation sweep, 2^24 perturbed identity fixpoints per noise level 1e0 .. 1e-9,
+        # <= 100 self-applications each; means next to the reference's logged values (100 trials per level)
+        dwk = eng.make_desc(eng.KIND_WW, 2, 2)
+        basefix = np.zeros(14, np.float32)
+        basefix[[0, 8, 12]] = 1.0
+        ref_y = [3.63, 5.02, 6.46, 8.04, 9.61, 11.23, 12.99, 14.58, 21.95, 26.45]
+        ref_z = [0, 0, 0, 0, 0.04, 1.38, 3.23, 4.84, 11.91, 16.47]
+        nt, scale, ys, zs, steps_total = 1 << 24, 1.0, [], [], 0.0
+        eng.kfv(dwk, basefix, nt, 1.0, 0, 100, 1e-4, seed=11, want_times=False)
+        t_kfv = 0.0
+        for level in range(10):
+            res = {}
+            t_kfv += _timed(torch, lambda: res.update(eng.kfv(dwk, basefix, nt, scale, level, 100, 1e-4, seed=11, want_times=False)))
+            h = res["hist"].cpu().numpy().astype(np.float64)
+            ys.append(float((h[0] * np.arange(101)).sum() / nt))
+            zs.append(float((h[1] * np.arange(101)).sum() / nt))
+            steps_total += float((h[0] * np.arange(101)).sum()) + nt
+            scale /= 10.0
+        out["kfv_sweep"] = {"metric": "known-fixpoint variation trials/sec", "value": 10 * nt / t_kfv, "unit": "trials/s",
+                            "config": {"workload": "kfv_sweep", "trials_per_level": nt, "levels": "1e0..1e-9", "max_steps": 100,
+                                       "epsilon": 1e-4},
+                            "self_applications_per_s": steps_total / t_kfv,
+                            "mean_steps_to_vergence": ys, "reference_log_steps_to_vergence": ref_y,
+                            "mean_steps_as_fixpoint": zs, "reference_log_steps_as_fixpoint": ref_z}
         # configs[1]: self-training, 10k WW + 10k AGG(4) x 1000 epochs; and a 2^20-net WW run for throughput
         dw, da = eng.make_desc(eng.KIND_WW, 2, 2), eng.make_desc(eng.KIND_AGG, 2, 2, 4)
         pw, pa = eng.Population(dw, 10_000).init(seed=1), eng.Population(da, 10_000).init(seed=1)
