@@ -620,8 +620,8 @@ int srnn_oracle_train(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, i
 
 /* ================================================================== known-fixpoint variation */
 /* code/setups/known-fixpoint-variation.py:37-46 (vary) and :60-89 (trial loop).  Deterministic
- * stand-in for Python's `random`: weight k of trial i uses rng4(ST_KFV, slot, level, k) words
- * (coin, magnitude): coin < 0.5 ? w + u*e : w - u*e in float64, stored as float32. */
+ * stand-in for Python's `random`: weights 2m, 2m+1 of trial i use words (0,1) and (2,3) of rng4(ST_KFV, slot, level, m)
+ * as (coin, magnitude): coin < 0.5 ? w + u*e : w - u*e in float64, stored as float32. */
 static inline double u01d(uint32_t x) { return (double)x * 2.3283064365386963e-10; } /* x / 2^32 */
 
 int srnn_oracle_kfv(const srnn_net_desc *d, const float *base /* n_weights */, int64_t n, double scale,
@@ -638,9 +638,9 @@ int srnn_oracle_kfv(const srnn_net_desc *d, const float *base /* n_weights */, i
             float cur[MAXW], nxt[MAXW];
             for (int k = 0; k < s.n_weights; ++k) {
                 uint32_t x[4];
-                rng4(seed, ST_KFV, slot0 + (uint64_t)i, level, (uint32_t)k, x);
-                double mag = u01d(x[1]) * scale;
-                double v = u01d(x[0]) < 0.5 ? (double)base[k] + mag : (double)base[k] - mag;
+                rng4(seed, ST_KFV, slot0 + (uint64_t)i, level, (uint32_t)(k >> 1), x);   /* one Philox block per 2 weights */
+                double mag = u01d(x[(k & 1) * 2 + 1]) * scale;
+                double v = u01d(x[(k & 1) * 2]) < 0.5 ? (double)base[k] + mag : (double)base[k] - mag;
                 cur[k] = (float)v;
             }
             int32_t tts = 0, taf = 0;

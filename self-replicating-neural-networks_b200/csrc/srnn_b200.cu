@@ -402,6 +402,10 @@ __global__ void __launch_bounds__(BS) train_kernel(float *__restrict__ w, int64_
 // ================================================================================================ K9 known-fixpoint variation
 struct BaseNet { float v[SRNN_MAX_WEIGHTS]; };
 
+// One thread per trial, the warp runs until its slowest lane ends.  (A variant that refills finished lanes with new
+// trials of a per-warp chunk -- ballot + prefix rank, batched refills -- was measured SLOWER, 5.5e10 vs 7.2e10
+// executed self-applications/s: starting a trial costs as much as several steps and the refill logic defeats the
+// straight-line step loop.)
 template <class S>
 __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, double scale, uint32_t level,
                                                  int max_steps, Eps eps, uint64_t seed, uint64_t slot0,
@@ -419,11 +423,14 @@ __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, dou
     float cur[S::NW], nxt[S::NW];
     // vary(), known-fixpoint-variation.py:37-46: float64 perturbation stored as float32
 #pragma unroll
-    for (int k = 0; k < S::NW; ++k) {
-        const U4 x = rng4(seed, ST_KFV, slot0 + (uint64_t)i, level, (uint32_t)k);
-        const double mag = __dmul_rn(u01d(x.y), scale);
-        const double b = (double)basenet.v[k];
-        cur[k] = (float)(u01d(x.x) < 0.5 ? __dadd_rn(b, mag) : __dsub_rn(b, mag));
+    for (int k = 0; k < S::NW; k += 2) {   // one Philox block per two weights
+        const U4 x = rng4(seed, ST_KFV, slot0 + (uint64_t)i, level, (uint32_t)(k >> 1));
+        const double m0 = __dmul_rn(u01d(x.y), scale), b0 = (double)basenet.v[k];
+        cur[k] = (float)(u01d(x.x) < 0.5 ? __dadd_rn(b0, m0) : __dsub_rn(b0, m0));
+        if (k + 1 < S::NW) {
+            const double m1 = __dmul_rn(u01d(x.w), scale), b1 = (double)basenet.v[k + 1];
+            cur[k + 1] = (float)(u01d(x.z) < 0.5 ? __dadd_rn(b1, m1) : __dsub_rn(b1, m1));
+        }
     }
     // trial loop :69-82; after each self_attack the fixpoint test's application is the next step's result
     bool still = true;
