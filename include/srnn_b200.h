@@ -135,8 +135,9 @@ int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w,
  * per-generation all-gather when sharded); this call owns particles [slot0, slot0+n) and writes their
  * new records to w_out (w_out must not alias snap).  Pairings are Philox draws of (seed, slot, gen) in the
  * reference's per-particle order; a victim hit several times applies attackers in ascending index.
- *   scratch  int32[n_total + 4*n + 16]: attack lists (head[n] | next[n_total]) and, for the multi-pass path taken
- *            by large soups, compacted victim / learner work lists, flags and counters; needs no initialisation
+ *   scratch  int32[n_total + 4*n + 16]: attack lists (head[n] | next[n_total]) and, for the opt-in variants
+ *            (params->engine_path 2 = multi-pass, 3 = persistent), work lists, flags, counters and the grid barrier
+ *            word; needs no initialisation
  *   action (nullable) uint8[n], loss (nullable) double[n], dead (nullable) uint8[n] (1 = respawned) */
 int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const float *snap, int64_t snap_ld,
                    int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed,
@@ -157,7 +158,8 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
 /* n_gens consecutive snapshot-synchronous generations (gen0, gen0+1, ...) of an UNSHARDED soup in one call, so a
  * small soup is not bound by the host's per-call overhead: generation gen0+g reads w_a and writes w_b for even g,
  * the other way round for odd g -- the newest arena is w_b if n_gens is odd, else w_a.  Same arguments and
- * semantics as srnn_soup_sync with n_total = n, slot0 = 0; action / dead (nullable) hold the LAST generation's. */
+ * semantics as srnn_soup_sync with n_total = n, slot0 = 0; action / dead (nullable) hold the LAST generation's.
+ * params->engine_path = 3 runs all generations as ONE persistent cooperative kernel (n <= 2^20); same results. */
 int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w_a, float *w_b, int64_t ld, int64_t n,
                        uint64_t seed, uint64_t gen0, int32_t n_gens, int32_t *scratch, uint8_t *action, uint8_t *dead,
                        void *stream);
@@ -185,7 +187,8 @@ int srnn_assign_uids_static(const uint8_t *dead, int64_t n, int64_t uid_base, in
 
 /* FP32 issue-rate probe: an FFMA-only kernel (independent chains, operands in registers) used as the
  * measured roofline denominator for the register-resident kernels (MEASURED_PEAKS.json has no FP32 entry).
- * Runs `iters` x 64 FFMA per thread over grid x block threads; out = float[grid*block] sink. */
+ * Runs |iters| x 64 FMA per thread over grid x block threads; out = float[grid*block] sink.  iters > 0: three-register
+ * FFMA; -2^24 < iters < 0: FFMA with an immediate operand; iters <= -2^24: packed FFMA2 (|iters| - 2^24 iterations). */
 int srnn_fp32_probe(float *out, int32_t grid, int32_t block, int32_t iters, void *stream);
 
 #ifdef __cplusplus
