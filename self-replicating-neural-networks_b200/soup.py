@@ -341,6 +341,7 @@ class PopulationSoup:
         self._n_dead = B.alloc((1,), torch.int64)
         self.next_uid = self.size
         self.track_uids = False
+        self._watch = None          # (local indices, every, {local index -> list of state dicts})
 
     @property
     def local(self):
@@ -371,8 +372,9 @@ class PopulationSoup:
                 self.rounds = B.soup_exact(self.desc, sp, self.w, self.seed, self.time, self._scratch, self.action, self.dead)
                 if self.track_uids:
                     self._assign_uids()
+                self._log_watched()
             return self
-        if self.world == 1 and not self.track_uids and iterations > 1 and hasattr(B, "soup_sync_run"):
+        if self.world == 1 and not self.track_uids and self._watch is None and iterations > 1 and hasattr(B, "soup_sync_run"):
             # unsharded: all generations in one C call (no per-generation host overhead)
             B.soup_sync_run(self.desc, sp, self.w, self._next, self.seed, self.time + 1, iterations, self._scratch,
                             self.action, self.dead)
@@ -393,6 +395,7 @@ class PopulationSoup:
                 self.w, self._next = self._next, self.w
                 if self.track_uids:
                     self._assign_uids()
+                self._log_watched()
                 continue
             if self.world > 1:
                 dist.all_gather_into_tensor(self._snap, self.w, group=self.group)   # NCCL over NVLink on the box
@@ -404,6 +407,7 @@ class PopulationSoup:
             self.w, self._next = self._next, self.w
             if self.track_uids:
                 self._assign_uids()
+            self._log_watched()
         return self
 
     def _assign_uids(self):
@@ -419,6 +423,40 @@ class PopulationSoup:
             counts = [int(mine.item())]
         base, self.next_uid = uid_base_of(self.rank, counts, self.next_uid)
         self.backend.assign_uids(self.dead, self.uid, base, self._uid_tmp, self._n_dead)
+
+    # ---- trajectory logging at scale: the reference logs every particle every generation
+    #      (code/soup.py:87); a 10 M-particle soup logs a chosen subset, every k-th generation, in the same schema
+    def watch(self, particles, every=1):
+        """Record the states of the given GLOBAL particle indices (those owned by this rank) every `every` generations.
+        Turns on uid tracking so respawned particles start a new trajectory under a new uid, as in the reference."""
+        import torch
+        mine = [int(g) - self.slot0 for g in particles if self.slot0 <= int(g) < self.slot0 + self.n_local]
+        self._watch = (torch.as_tensor(mine, dtype=torch.int64, device=self.w.device), int(every), {})
+        self.track_uids = True
+        self._log_watched(first=True)
+        return self
+
+    def _log_watched(self, first=False):
+        if self._watch is None or (not first and self.time % self._watch[1]):
+            return
+        idx, _, log = self._watch
+        if idx.numel() == 0:
+            return
+        w = self.w[idx, :self.desc.n_weights].cpu().numpy()
+        uid = self.uid[idx].cpu().numpy()
+        act = self.action[idx].cpu().numpy()
+        name = _eng.KIND_NAMES[self.desc.kind]
+        for row in range(idx.numel()):
+            if not np.isfinite(w[row]).all():          # ParticleDecorator.make_state drops non-finite states
+                continue
+            state = {'class': name, 'weights': w[row].copy(), 'time': self.time,
+                     'action': 'init' if first else _eng.ACT_NAMES[int(act[row])], 'counterpart': None}
+            log.setdefault(int(uid[row]), []).append(state)
+
+    def historical_particles(self):
+        """uid -> list of state dicts for the watched particles: the structure Soup.without_particles() pickles and the
+        reference's visualization.py reads (code/visualization.py:27-40)."""
+        return {} if self._watch is None else self._watch[2]
 
     # ---- checkpoint / resume (the reference can only dill-dump finished experiments, code/experiment.py:56-59)
     def state_dict(self):

@@ -381,3 +381,31 @@ def test_persistent_soup_equals_per_generation_launches(api, kind, n, gens):
     b.evolve(1)
     assert_same_weights(a.local.numpy(), b.local.numpy())
 
+
+def test_population_soup_watch_trajectories(api, tmp_path, monkeypatch):
+    """Trajectory logging at scale: watched particles of a PopulationSoup produce the reference's state-dict schema
+    (uid -> [{class, weights, time, action, counterpart}]), respawns start a new uid, and the result pickles through
+    Experiment.save like the reference's soups."""
+    network, soup_mod, experiment = api
+    import srnn_engine as eng
+    monkeypatch.chdir(tmp_path)
+    n = 2000
+    s = soup_mod.PopulationSoup(eng.KIND_WW, n, seed=5, attacking_rate=0.5, learn_from_rate=0.1, train=0,
+                                remove_divergent=True, remove_zero=True).seed_particles()
+    s.watch(range(0, n, 100), every=2)
+    s.evolve(10)
+    hp = s.historical_particles()
+    assert len(hp) >= 20                                  # 20 watched slots, plus new uids for respawned ones
+    assert any(uid >= n for uid in hp)                    # with attack 0.5 and no training, some watched particle died
+    for uid, states in hp.items():
+        times = [st['time'] for st in states]
+        assert times == sorted(times) and all(t % 2 == 0 for t in times)
+        for st in states:
+            assert set(st) == {'class', 'weights', 'time', 'action', 'counterpart'}
+            assert st['class'] == 'WeightwiseNeuralNetwork' and st['weights'].shape == (14,)
+            assert st['action'] in ('init', None, 'attacking', 'learn_from', 'train_self', 'divergent_dead', 'zweo_dead')
+    with experiment.SoupExperiment("population-soup") as exp:
+        exp.save(soup_states=hp)
+    back = experiment.Experiment.from_dill(os.path.join(exp.dir, "soup_states.dill"))
+    assert set(back) == set(hp)
+
