@@ -360,15 +360,17 @@ def test_population_soup_checkpoint_resume(api, tmp_path):
 
 
 @pytest.mark.parametrize("kind,n,gens", [(0, 5000, 7), (1, 3000, 4), (2, 2000, 3), (0, 300_000, 5)])
-def test_persistent_soup_equals_per_generation_launches(api, kind, n, gens):
-    """engine_path=3: evolve(k) of an unsharded soup as ONE persistent cooperative launch (grid barriers between
-    generations); it must equal k single-generation launches bit for bit -- also with more tiles than resident CTAs."""
+@pytest.mark.parametrize("path", [0, 3])
+def test_multi_generation_runs_equal_per_generation_launches(api, kind, n, gens, path):
+    """evolve(k) of an unsharded soup: engine_path=0 chains the generations (one launch each, next generation's attack
+    lists built by the previous launch), engine_path=3 is ONE persistent cooperative launch with grid barriers.  Both
+    must equal k single-generation launches bit for bit -- also with more tiles than resident CTAs."""
     network, soup_mod, _ = api
     import srnn_engine as eng
     kw = dict(seed=21, aggregates=4 if kind == 1 else 0, attacking_rate=0.3, learn_from_rate=0.2, train=1,
               learn_from_severity=2, remove_divergent=True, remove_zero=True, epsilon=1e-4)
-    a = soup_mod.PopulationSoup(kind, n, engine_path=3, **kw).seed_particles()
-    a.evolve(gens)                                        # persistent kernel
+    a = soup_mod.PopulationSoup(kind, n, engine_path=path, **kw).seed_particles()
+    a.evolve(gens)                                        # chained / persistent
     b = soup_mod.PopulationSoup(kind, n, engine_path=1, **kw).seed_particles()
     for _ in range(gens):
         b.evolve(1)                                       # one fused launch per generation
