@@ -229,7 +229,28 @@ __global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restric
     float cur[S::NW], nxt[S::NW];
     tile_load<S::NW>(w, ld, base, n, tile, cur);
     int it = 0, cls = SRNN_CLS_OTHER;
-    if (active) {
+    if (active && mode == SRNN_RUN_FIXED && !traj) {
+        // applying-fixpoints.py flow (n_steps x self_attack, then count): the bare ping-pong loop of the fixed kernel,
+        // and one more application afterwards for the classifier's fixpoint test
+        const float one = opaque_one();
+        int s = 0;
+        for (; s + 2 <= n_steps; s += 2) {
+            net_apply<S>(cur, cur, nxt, one);
+            net_apply<S>(nxt, nxt, cur, one);
+        }
+        if (s < n_steps) {
+            net_apply<S>(cur, cur, nxt, one);
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
+        }
+        it = n_steps;
+        if (steps_out) steps_out[i] = it;
+        if (cls_out || counters) {
+            net_apply<S>(cur, cur, nxt, one);
+            cls = classify_with<S>(cur, nxt, eps.ge, eps.le, with_fix_sec);
+            if (cls_out) cls_out[i] = (uint8_t)cls;
+        }
+    } else if (active) {
         net_apply<S>(cur, cur, nxt, opaque_one());  // look-ahead: is_fixpoint's application IS the next self_attack
         while (it < n_steps) {
             if (mode == SRNN_RUN_UNTIL && (is_diverged<S::NW>(cur) || is_close<S::NW>(nxt, cur, eps.ge))) break;
