@@ -562,3 +562,41 @@ def test_population_soup_exact_mode(eng):
         assert_same_weights(s.local.numpy(), ref, "generation %d" % gen)
     assert s.rounds >= 2 and sum(s.count().values()) == n
 
+
+def test_full_size_soup_properties(eng):
+    """A 2^22-particle soup generation (the 10 M-particle regime): (i) one owner == three uneven owners == the multi-pass
+    path, bit for bit; (ii) two slices of the result equal the oracle's computation of those slices from the full
+    snapshot; (iii) every particle is accounted for in the action histogram."""
+    import torch
+    dg, do = both(eng, (0, 2, 2, 0))
+    n = 1 << 22
+    kw = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pop = eng.Population(dg, n).init(seed=77)
+    pop.self_apply(2)                                    # some nets already tiny / huge, so culling happens
+    snap = pop.w
+    scratch = torch.zeros(eng.soup_scratch_len(n, n), dtype=torch.int32, device="cuda")
+    out = torch.zeros_like(snap)
+    action = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    eng.soup_sync(dg, eng.make_soup_params(**kw), snap, n, out, 0, n, 5, 1, scratch, action=action)
+    # (i) sharding and path invariance
+    cuts = [0, n // 3 + 11, 2 * n // 3 - 5, n]
+    o2 = torch.zeros_like(snap)
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        eng.soup_sync(dg, eng.make_soup_params(**kw), snap, n, o2[a:b], a, b - a, 5, 1, scratch)
+    assert torch.equal(o2.view(torch.int32), out.view(torch.int32))
+    o3 = torch.zeros_like(snap)
+    eng.soup_sync(dg, eng.make_soup_params(engine_path=2, **kw), snap, n, o3, 0, n, 5, 1, scratch)
+    assert torch.equal(o3.view(torch.int32), out.view(torch.int32))
+    # (ii) oracle on two slices of the full snapshot
+    snap_h = snap.cpu().numpy()
+    po = oracle.soup_params(**kw)
+    for slot0 in (0, n - 5000):
+        ref = np.zeros((5000, 14), np.float32)
+        ra, _, _ = oracle.soup_sync(do, po, snap_h, n, ref, slot0, 5000, 5, 1)
+        assert_same_weights(out[slot0:slot0 + 5000].cpu().numpy(), ref, "slice at %d" % slot0)
+        assert np.array_equal(action[slot0:slot0 + 5000].cpu().numpy(), ra)
+    # (iii) action histogram
+    hist = torch.bincount(action.to(torch.int64), minlength=6).cpu().numpy()
+    assert hist.sum() == n and hist[3] == 0 and 0.05 * n < hist[1] + hist[2] < 0.3 * n
+
