@@ -129,26 +129,31 @@ __device__ __forceinline__ void tile_put(float *tile, int r, const float *reg) {
     }
 }
 // whole-tile staging, HBM -> shared (any record stride)
-template <int NW, int NT, bool CG = false>
+// NT threads stage TILE consecutive records (TILE a multiple of NT)
+template <int NW, int NT, bool CG = false, int TILE = NT>
 __device__ __forceinline__ void tile_stage_in(const float *__restrict__ w, int64_t ld, int64_t base, int64_t n, float *tile) {
-    const int cnt = (int)min((int64_t)NT, n - base);
+    const int cnt = (int)max((int64_t)0, min((int64_t)TILE, n - base));
     if (ld == NW) {
         flat_copy<NT, CG>(tile, w + base * NW, cnt * NW);
-    } else if ((int)threadIdx.x < cnt) {
-        const float *src = w + (base + threadIdx.x) * ld;
+    } else {
+        for (int v = threadIdx.x; v < cnt; v += NT) {
+            const float *src = w + (base + v) * ld;
 #pragma unroll
-        for (int k = 0; k < NW; ++k) tile[threadIdx.x * NW + k] = CG ? __ldcg(src + k) : __ldg(src + k);
+            for (int k = 0; k < NW; ++k) tile[v * NW + k] = CG ? __ldcg(src + k) : __ldg(src + k);
+        }
     }
 }
-template <int NW, int NT>
+template <int NW, int NT, int TILE = NT>
 __device__ __forceinline__ void tile_stage_out(float *__restrict__ w, int64_t ld, int64_t base, int64_t n, const float *tile) {
-    const int cnt = (int)min((int64_t)NT, n - base);
+    const int cnt = (int)max((int64_t)0, min((int64_t)TILE, n - base));
     if (ld == NW) {
         flat_copy<NT>(w + base * NW, tile, cnt * NW);
-    } else if ((int)threadIdx.x < cnt) {
-        float *dst = w + (base + threadIdx.x) * ld;
+    } else {
+        for (int v = threadIdx.x; v < cnt; v += NT) {
+            float *dst = w + (base + v) * ld;
 #pragma unroll
-        for (int k = 0; k < NW; ++k) dst[k] = tile[threadIdx.x * NW + k];
+            for (int k = 0; k < NW; ++k) dst[k] = tile[v * NW + k];
+        }
     }
 }
 // tile + registers in one go (the register-resident kernels)
@@ -730,8 +735,26 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 // COMPACTED into a queue and handed to the first threads of the CTA, so whole warps skip a phase instead of every
 // warp executing every path for one or two of its lanes.  Results do not depend on who processes a particle.
 #ifndef SRNN_SOUP_MINB
-#define SRNN_SOUP_MINB 10
+#define SRNN_SOUP_MINB 6   // x 128 threads x 2 particles = 1536 particles per SM (shared memory allows no more)
 #endif
+// Each thread OWNS PPT particles of the tile (particle tid + r*SBS) for the uniform work -- staging, pairing draw,
+// training, cull test -- so the loads and the arithmetic of PPT particles overlap inside one thread and the
+// per-tile barriers are paid once per 256 particles; the compacted queues are worked off by the first threads as
+// before.  Measured on B200, 10 M particles: PPT 1 (10 CTAs/SM) 0.78 ms, PPT 2 (6) 0.68 ms, PPT 3 (4) 0.70 ms per
+// generation; with train=1: 1.08 / 1.01 / 1.06 ms (profiles/r01_soup_ppt_ab.txt).
+#ifndef SRNN_SOUP_PPT
+#define SRNN_SOUP_PPT 2
+#endif
+// shared memory of one CTA: tile + two partner-prefetch areas (TILE/4 records each) + queues (static) and the
+// per-thread SGD scratch (dynamic); shapes whose records are too large for 48 KB keep one particle per thread
+__host__ __device__ constexpr int soup_static_smem(int nw, int ppt) { return nw * 4 * SOUP_BS * ppt * 3 / 2 + 9 * SOUP_BS * ppt + 64; }
+template <class S>
+__host__ __device__ constexpr int soup_ppt() {
+    return soup_static_smem(S::NW, SRNN_SOUP_PPT) + (int)sgd_smem_bytes<S>(SOUP_BS) <= 48 * 1024 ? SRNN_SOUP_PPT : 1;
+}
+template <class S>
+__host__ __device__ constexpr int soup_tile() { return SOUP_BS * soup_ppt<S>(); }   // particles per CTA
+
 template <class S, int SBS, bool CG>
 __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const ShardTable &snap, const float *own,
                                                      int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld,
@@ -739,65 +762,78 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
                                                      const Limits &lim, const int32_t *head, const int32_t *next,
                                                      uint8_t *action, double *loss, uint8_t *dead_out) {
     extern __shared__ __align__(16) unsigned char smem[];
-    constexpr int NW = S::NW;
-    constexpr int QCAP = SBS / 4;   // partner records prefetched per phase and tile (mean SBS/10); beyond: slow path
-    __shared__ __align__(16) float tile[SBS * NW];
+    constexpr int NW = S::NW, PPT = soup_ppt<S>(), TILE = SBS * PPT;
+    constexpr int QCAP = TILE / 4;   // partner records prefetched per phase and tile (mean TILE/10); beyond: slow path
+    __shared__ __align__(16) float tile[TILE * NW];
     __shared__ __align__(16) float att_s[QCAP * NW];   // the first attacker's record of each queued victim
     __shared__ __align__(16) float tch_s[QCAP * NW];   // the teacher's record of each queued learner
-    __shared__ int32_t lrn_s[SBS];
-    __shared__ uint16_t queue[SBS], queue_l[SBS];
+    __shared__ int32_t lrn_s[TILE];
+    __shared__ uint16_t queue[TILE], queue_l[TILE];
     __shared__ uint8_t single_s[QCAP];
     __shared__ int q_len, ql_len;
     const int tid = threadIdx.x;
-    const int64_t base = tile_idx * SBS, i = base + tid;
-    const bool active = i < n;
+    const int64_t base = tile_idx * TILE;
     const int sev = p.severity > 0 ? p.severity : 0, tr = p.train > 0 ? p.train : 0;
     const uint64_t ep = gen * (uint64_t)(sev + tr);
     const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
     SgdScratch sc = sgd_scratch<S>(smem, SBS);
     // ---- everything that only needs the particle index is issued up front so the DRAM latencies overlap:
-    //      the list head, the tile staging, the pairing draw
-    const int32_t my_head = active ? (CG ? __ldcg(head + i) : __ldg(head + i)) : -1;
-    tile_stage_in<NW, SBS, CG>(own, snap_ld, base, n, tile);
+    //      the list heads, the tile staging, the pairing draws
+    int32_t my_head[PPT];
+    int64_t at[PPT], lr[PPT];
+#pragma unroll
+    for (int r = 0; r < PPT; ++r) {
+        const int64_t i = base + tid + r * SBS;
+        my_head[r] = i < n ? (CG ? __ldcg(head + i) : __ldg(head + i)) : -1;
+    }
+    tile_stage_in<NW, SBS, CG, TILE>(own, snap_ld, base, n, tile);
     if (tid == 0) { q_len = 0; ql_len = 0; }
-    int64_t at = -1, lr = -1;
-    if (active) soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at, &lr);
-    lrn_s[tid] = (int32_t)lr;
+#pragma unroll
+    for (int r = 0; r < PPT; ++r) {
+        const int64_t i = base + tid + r * SBS;
+        at[r] = -1; lr[r] = -1;
+        if (i < n) soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at[r], &lr[r]);
+        lrn_s[tid + r * SBS] = (int32_t)lr[r];
+    }
     __syncthreads();
     // ---- owners enqueue their events and, in the memory-latency-bound regime (no self-training in the generation),
     //      PREFETCH the partner records into shared memory: one DRAM round trip for attackers and teachers together
     //      instead of one per serial phase (-9 % at 10 M particles; with training the extra instructions cost more
     //      than the latency they hide, so there the partners are fetched inside the phases)
     const bool prefetch = tr == 0;
-    if (my_head >= 0) {
-        const int qa = atomicAdd(&q_len, 1);
-        queue[qa] = (uint16_t)tid;
-        if (prefetch && qa < QCAP) {
-            const int32_t nx = CG ? __ldcg(next + my_head) : __ldg(next + my_head);
-            const float *rec = shard_record(snap, snap_ld, my_head);
 #pragma unroll
-            for (int k = 0; k < NW; ++k) att_s[qa * NW + k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
-            single_s[qa] = nx < 0;
+    for (int r = 0; r < PPT; ++r) {
+        const int v = tid + r * SBS;
+        if (my_head[r] >= 0) {
+            const int qa = atomicAdd(&q_len, 1);
+            queue[qa] = (uint16_t)v;
+            if (prefetch && qa < QCAP) {
+                const int32_t nx = CG ? __ldcg(next + my_head[r]) : __ldg(next + my_head[r]);
+                const float *rec = shard_record(snap, snap_ld, my_head[r]);
+#pragma unroll
+                for (int k = 0; k < NW; ++k) att_s[qa * NW + k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
+                single_s[qa] = nx < 0;
+            }
         }
-    }
-    if (active && lr >= 0 && sev > 0) {
-        const int ql = atomicAdd(&ql_len, 1);
-        queue_l[ql] = (uint16_t)tid;
-        if (prefetch && ql < QCAP) {
-            const float *rec = shard_record(snap, snap_ld, lr);
+        if (lr[r] >= 0 && sev > 0) {
+            const int ql = atomicAdd(&ql_len, 1);
+            queue_l[ql] = (uint16_t)v;
+            if (prefetch && ql < QCAP) {
+                const float *rec = shard_record(snap, snap_ld, lr[r]);
 #pragma unroll
-            for (int k = 0; k < NW; ++k) tch_s[ql * NW + k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
+                for (int k = 0; k < NW; ++k) tch_s[ql * NW + k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
+            }
         }
     }
     __syncthreads();
     // ---- phase 1: particles hit by attackers (code/soup.py:56-61 seen from the victim)
-    if (tid < q_len) {
-        const int v = queue[tid];
+    for (int q = tid; q < q_len; q += SBS) {
+        const int v = queue[q];
         float cur[NW];
         tile_get<NW>(tile, v, cur);
-        if (prefetch && tid < QCAP && single_s[tid]) {   // the usual case: exactly one attacker, already in shared memory
+        if (prefetch && q < QCAP && single_s[q]) {   // the usual case: exactly one attacker, already in shared memory
             float op[NW], res[NW];
-            tile_get<NW>(att_s, tid, op);
+            tile_get<NW>(att_s, q, op);
             net_apply<S>(op, cur, res, sc.one);
             tile_put<NW>(tile, v, res);
         } else {
@@ -807,13 +843,13 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     }
     __syncthreads();
     // ---- phase 2: learn_from x severity (code/soup.py:62-68), teacher read from the snapshot
-    if (tid < ql_len) {
-        const int v = queue_l[tid];
+    for (int q = tid; q < ql_len; q += SBS) {
+        const int v = queue_l[q];
         float cur[NW];
         tile_get<NW>(tile, v, cur);
-        if (prefetch && tid < QCAP) {
+        if (prefetch && q < QCAP) {
 #pragma unroll
-            for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = tch_s[tid * NW + k];
+            for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = tch_s[q * NW + k];
         } else {
             const float *rec = shard_record(snap, snap_ld, lrn_s[v]);
 #pragma unroll
@@ -827,45 +863,58 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     }
     __syncthreads();
     // ---- phase 3: self-training (every particle, code/soup.py:69-76) and the cull tests (:77-86)
-    float cur[NW];
-    tile_get<NW>(tile, tid, cur);
-    double ls = nan("");
-    int dead = 0;
-    if (active) {
-        for (int e = 0; e < tr; ++e) {
+    double ls[PPT];
+    int dead[PPT];
 #pragma unroll
-            for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = cur[k];
-            if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + i), ep + (uint64_t)(sev + e), sc.ord, sc.stride);
-            ls = train_epoch<S>(cur, sc, ordered, p.lr);
+    for (int r = 0; r < PPT; ++r) {
+        const int v = tid + r * SBS;
+        const int64_t i = base + v;
+        ls[r] = nan("");
+        dead[r] = 0;
+        if (i < n) {
+            float cur[NW];
+            tile_get<NW>(tile, v, cur);
+            for (int e = 0; e < tr; ++e) {
+#pragma unroll
+                for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+                if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + i), ep + (uint64_t)(sev + e), sc.ord, sc.stride);
+                ls[r] = train_epoch<S>(cur, sc, ordered, p.lr);
+            }
+            if (tr > 0) tile_put<NW>(tile, v, cur);
+            if (p.remove_divergent && is_diverged<NW>(cur)) dead[r] = SRNN_ACT_DIV_DEAD;
+            if (p.remove_zero && is_zero<NW>(cur, p.eps.le)) dead[r] = SRNN_ACT_ZERO_DEAD;
         }
-        if (tr > 0) tile_put<NW>(tile, tid, cur);
-        if (p.remove_divergent && is_diverged<NW>(cur)) dead = SRNN_ACT_DIV_DEAD;
-        if (p.remove_zero && is_zero<NW>(cur, p.eps.le)) dead = SRNN_ACT_ZERO_DEAD;
     }
     if (tid == 0) q_len = 0;
     __syncthreads();
     // ---- phase 4: respawn (generate_particle): a pure function of (seed, slot, generation)
-    if (dead) queue[atomicAdd(&q_len, 1)] = (uint16_t)tid;
+#pragma unroll
+    for (int r = 0; r < PPT; ++r)
+        if (dead[r]) queue[atomicAdd(&q_len, 1)] = (uint16_t)(tid + r * SBS);
     __syncthreads();
-    if (tid < q_len) {
-        const int v = queue[tid];
+    for (int q = tid; q < q_len; q += SBS) {
+        const int v = queue[q];
         float fresh[NW];
         init_net<S>(seed, (uint64_t)(slot0 + base + v), (uint32_t)gen, lim, fresh);
         tile_put<NW>(tile, v, fresh);
     }
-    if (active) {
-        uint8_t act = SRNN_ACT_NONE;
-        if (at >= 0) act = SRNN_ACT_ATTACK;
-        if (lr >= 0) act = SRNN_ACT_LEARN;
-        if (tr > 0) act = SRNN_ACT_TRAIN;
-        if (dead) act = (uint8_t)dead;
-        if (action) action[i] = act;
-        if (loss) loss[i] = ls;
-        if (dead_out) dead_out[i] = dead ? 1 : 0;
+#pragma unroll
+    for (int r = 0; r < PPT; ++r) {
+        const int64_t i = base + tid + r * SBS;
+        if (i < n) {
+            uint8_t act = SRNN_ACT_NONE;
+            if (at[r] >= 0) act = SRNN_ACT_ATTACK;
+            if (lr[r] >= 0) act = SRNN_ACT_LEARN;
+            if (tr > 0) act = SRNN_ACT_TRAIN;
+            if (dead[r]) act = (uint8_t)dead[r];
+            if (action) action[i] = act;
+            if (loss) loss[i] = ls[r];
+            if (dead_out) dead_out[i] = dead[r] ? 1 : 0;
+        }
     }
     __syncthreads();
     // ---- write the new generation
-    tile_stage_out<NW, SBS>(w_out, out_ld, base, n, tile);
+    tile_stage_out<NW, SBS, TILE>(w_out, out_ld, base, n, tile);
 }
 
 template <class S, int SBS>
@@ -895,13 +944,16 @@ __global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_chain_kernel(const f
     tab.n = 1;
     soup_tile_generation<S, SBS, false>(blockIdx.x, tab, src, ld, n, dst, ld, 0, n, p, seed, gen, lim, head_cur, next_cur,
                                         action, nullptr, dead_out);
-    const int64_t i = (int64_t)blockIdx.x * SBS + threadIdx.x;
-    if (i < n) {
-        head_cur[i] = -1;   // only this CTA reads its heads, and it is done with them
-        if (make_next && p.attacking_rate > 0.0) {
-            int64_t at, lr;
-            soup_draw(p, seed, (uint64_t)i, gen + 1, n, &at, &lr);
-            if (at >= 0) next_nxt[i] = atomicExch(&head_nxt[at], (int32_t)i);
+#pragma unroll
+    for (int r = 0; r < soup_ppt<S>(); ++r) {
+        const int64_t i = (int64_t)blockIdx.x * soup_tile<S>() + threadIdx.x + r * SBS;
+        if (i < n) {
+            head_cur[i] = -1;   // only this CTA reads its heads, and it is done with them
+            if (make_next && p.attacking_rate > 0.0) {
+                int64_t at, lr;
+                soup_draw(p, seed, (uint64_t)i, gen + 1, n, &at, &lr);
+                if (at >= 0) next_nxt[i] = atomicExch(&head_nxt[at], (int32_t)i);
+            }
         }
     }
 }
@@ -931,7 +983,7 @@ __global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_persistent_kernel(fl
                                                                              uint8_t *dead_out, unsigned *barrier) {
     unsigned target = 0;
     const int64_t gtid = (int64_t)blockIdx.x * SBS + threadIdx.x, gsize = (int64_t)gridDim.x * SBS;
-    const int64_t n_tiles = (n + SBS - 1) / SBS;
+    const int64_t n_tiles = (n + soup_tile<S>() - 1) / soup_tile<S>();
     for (int64_t i = gtid; i < n; i += gsize) head[i] = -1;
     grid_barrier(barrier, target);
     for (int g = 0; g < n_gens; ++g) {
@@ -953,8 +1005,11 @@ __global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_persistent_kernel(fl
         for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
             soup_tile_generation<S, SBS, true>(t, tab, src, ld, n, dst, ld, 0, n, p, seed, gen, lim, head, next,
                                                last ? action : nullptr, nullptr, last ? dead_out : nullptr);
-            const int64_t i = t * SBS + threadIdx.x;
-            if (i < n) head[i] = -1;   // consumed: ready for the next generation's lists
+#pragma unroll
+            for (int r = 0; r < soup_ppt<S>(); ++r) {
+                const int64_t i = t * soup_tile<S>() + threadIdx.x + r * SBS;
+                if (i < n) head[i] = -1;   // consumed: ready for the next generation's lists
+            }
             __syncthreads();           // the shared tile is reused by the next tile of this CTA
         }
         grid_barrier(barrier, target);
@@ -1578,7 +1633,7 @@ static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, con
     if (snap_ld < S::NW || out_ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s"); \
     constexpr int SBS = SOUP_BS;                                                                             \
     const size_t sm = sgd_smem_bytes<S>(SBS);                                                                \
-    soup_sync_kernel<S, SBS><<<(unsigned)((n + SBS - 1) / SBS), SBS, sm, (cudaStream_t)stream>>>(            \
+    soup_sync_kernel<S, SBS><<<(unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>()), SBS, sm, (cudaStream_t)stream>>>( \
         tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead);
     SRNN_DISPATCH(d)
 #undef BODY
@@ -1698,7 +1753,7 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);                                       \
     ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, soup_persistent_kernel<S, SBS>, SBS, sm);    \
     if (ce != cudaSuccess || per_sm < 1) return fail(SRNN_ERR_CUDA, "occupancy query: %s", cudaGetErrorString(ce)); \
-    const int64_t tiles = (n + SBS - 1) / SBS;                                                               \
+    const int64_t tiles = (n + soup_tile<S>() - 1) / soup_tile<S>();                                                   \
     const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)per_sm * sms);                         \
     void *args[] = {&w_a, &w_b, &ld, &n, &q, &seed, &gen0, &nn_gens, &lim, &head, &next, &action, &dead, &barrier}; \
     ce = cudaLaunchCooperativeKernel((void *)soup_persistent_kernel<S, SBS>, dim3(grid), dim3(SBS), args, sm, st); \
@@ -1732,7 +1787,7 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
 #define BODY(S)                                                                                              \
     if (ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");                \
     constexpr int SBS = SOUP_BS;                                                                             \
-    soup_chain_kernel<S, SBS><<<(unsigned)((n + SBS - 1) / SBS), SBS, sgd_smem_bytes<S>(SBS), st>>>(          \
+    soup_chain_kernel<S, SBS><<<(unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>()), SBS, sgd_smem_bytes<S>(SBS), st>>>( \
         src, ld, dst, n, q, seed, gen, lim, hc, nc, hn, nn, last ? action : nullptr, last ? dead : nullptr, last ? 0 : 1);
             SRNN_DISPATCH(d)
 #undef BODY

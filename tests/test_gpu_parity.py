@@ -337,6 +337,35 @@ def test_soup_sync_bitwise_and_shard_invariance(eng, key, train, sev, path):
         snap, ref = out, rout
 
 
+@pytest.mark.parametrize("key", SHAPES)
+@pytest.mark.parametrize("n", [1, 255, 256, 257, 1000])
+def test_soup_sync_every_fast_shape_and_ragged_tiles(eng, key, n):
+    """Every compiled shape (the tile holds 128 or 256 particles depending on the record size) and particle counts
+    on both sides of the tile boundaries, through both the per-generation call and the chained run."""
+    import torch
+    dg, do = both(eng, key)
+    kw = dict(attacking_rate=0.5, learn_from_rate=0.3, train=1, learn_from_severity=1, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population(key, n, seed=5)
+    ref = w.copy()
+    snap = torch.from_numpy(w).cuda()
+    a, b = snap.clone(), torch.zeros_like(snap)
+    scratch = torch.zeros(eng.soup_scratch_len(n, n), dtype=torch.int32, device="cuda")
+    gens = 3
+    for gen in range(1, gens + 1):
+        out = torch.zeros_like(snap)
+        eng.soup_sync(dg, pg, snap, n, out, 0, n, 9, gen, scratch)
+        rout = np.zeros_like(ref)
+        oracle.soup_sync(do, po, ref, n, rout, 0, n, 9, gen)
+        assert_same_weights(out.cpu().numpy(), rout, "n %d gen %d" % (n, gen))
+        snap, ref = out, rout
+    scratch.zero_()
+    eng.soup_sync_run(dg, pg, a, b, 9, 1, gens, scratch)
+    last = b if gens % 2 else a
+    assert torch.equal(last.view(torch.int32), snap.view(torch.int32))
+
+
 # ---------------------------------------------------------------- full-size, size-independent properties
 def test_full_size_properties(eng):
     """2^22 WW(2,2) nets x 100 steps (the bench workload's shape): (i) the identity fixpoint is invariant,
