@@ -738,10 +738,12 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 #define SRNN_SOUP_MINB 6   // x 128 threads x 2 particles = 1536 particles per SM (shared memory allows no more)
 #endif
 // Each thread OWNS PPT particles of the tile (particle tid + r*SBS) for the uniform work -- staging, pairing draw,
-// training, cull test -- so the loads and the arithmetic of PPT particles overlap inside one thread and the
-// per-tile barriers are paid once per 256 particles; the compacted queues are worked off by the first threads as
-// before.  Measured on B200, 10 M particles: PPT 1 (10 CTAs/SM) 0.78 ms, PPT 2 (6) 0.68 ms, PPT 3 (4) 0.70 ms per
-// generation; with train=1: 1.08 / 1.01 / 1.06 ms (profiles/r01_soup_ppt_ab.txt).
+// training, cull test -- so the per-tile barriers are paid once per 256 particles and the compacted queues fill a
+// whole warp (about 25 events per phase instead of 12).  77 registers, no spills, 6 CTAs = 1536 particles per SM.
+// Same-box A/B against one particle per thread at 10 CTAs/SM (48 registers, 40 B of spills), 10 M particles,
+// ms per generation: attack .1 + learn .1: 0.664 -> 0.677 (train 0), 1.006 -> 1.012 (train 1); attack .3:
+// 0.700 -> 0.661; 1 M particles: 0.077 -> 0.074 / 0.111 -> 0.108.  A wash at the default rates, better where the
+// event rates are higher; three particles per thread are slower (profiles/r01_soup_ppt_ab.txt).
 #ifndef SRNN_SOUP_PPT
 #define SRNN_SOUP_PPT 2
 #endif

@@ -13,7 +13,9 @@ gens = int(sys.argv[2]) if len(sys.argv) > 2 else 6
 train = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 path = int(sys.argv[4]) if len(sys.argv) > 4 else 0   # 0 auto, 1 fused kernel, 2 multi-pass, 3 persistent
 order = sys.argv[5] if len(sys.argv) > 5 else "snapshot"   # or "exact"
-s = PopulationSoup(eng.KIND_WW, n, seed=4, attacking_rate=0.1, learn_from_rate=0.1, train=train, remove_divergent=True,
+ar = float(os.environ.get("PROF_ATTACK", "0.1"))   # rates overridable for phase-cost breakdowns
+lfr = float(os.environ.get("PROF_LEARN", "0.1"))
+s = PopulationSoup(eng.KIND_WW, n, seed=4, attacking_rate=ar, learn_from_rate=lfr, train=train, remove_divergent=True,
                    remove_zero=True, epsilon=1e-4, engine_path=path, order=order).seed_particles()
 s.evolve(2)
 torch.cuda.synchronize()
@@ -22,5 +24,5 @@ e0.record()
 s.evolve(gens)
 e1.record()
 e1.synchronize()
-print("particles %d train %d path %d order %s: %.3f ms / generation (rounds %d)" % (n, train, path, order,
+print("attack %g learn %g" % (ar, lfr), "particles %d train %d path %d order %s: %.3f ms / generation (rounds %d)" % (n, train, path, order,
       e0.elapsed_time(e1) / gens, s.rounds), s.count())
