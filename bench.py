@@ -239,14 +239,48 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
                                                              "partner records + list heads)",
                                         "traffic_source": "ncu dram bytes of one launch at 10 M particles (1.05 GB read + 0.59 GB write)"}}
         del s
-        # configs[4]: known-fixpoint variation sweep, 2^24 perturbed identity fixpoints per noise level 1e0 .. 1e-9,
+        # configs[2] variant of soup_trajectorys.py:22-24: 30 self-train epochs per particle and generation
+        kw30 = dict(attacking_rate=0.1, learn_from_rate=-1, train=30, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+        s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, **kw30).seed_particles()
+        s.evolve(5)
+        dt = _timed(torch, lambda: s.evolve(100))
+        out["soup_train30"] = {"metric": "soup generations/sec", "value": 100 / dt, "unit": "generations/s",
+                               "config": dict(workload="soup_100k_ww_train30", particles=100_000, generations=100, **kw30),
+                               "self_train_epochs_per_s": 100_000 * 30 * 100 / dt, "classes_after": s.count()}
+        del s
+        # configs[0/1] side figures: the size sweep 2^20 .. 2^27 nets (fresh glorot nets, 100 unconditional steps) and the
+        # early-stop variant (run_net's stop rule, experiment.py:70-77: stop at divergence or fixpoint), which executes
+        # fewer applications per net; both device-timed, one launch each
+        dww = eng.make_desc(eng.KIND_WW, 2, 2)
+        sweep = {}
+        for lg in range(20, 28):
+            pop = eng.Population(dww, 1 << lg).init(seed=lg)
+            if lg == 20:
+                pop.self_apply(N_STEPS)
+                pop.init(seed=lg)
+            sweep["2^%d" % lg] = (1 << lg) * N_STEPS / _timed(torch, lambda: pop.self_apply(N_STEPS))
+            del pop
+        out["size_sweep"] = {"metric": METRIC, "unit": UNIT, "values": sweep}
+        es = {}
+        for eps in (1e-14, 1e-4):
+            pop = eng.Population(dww, N_NETS).init(seed=0)
+            res = {}
+            dt = _timed(torch, lambda: res.update(pop.self_apply(N_STEPS, mode=eng.RUN_UNTIL, eps=eps, want_steps=True,
+                                                                 want_counters=True)))
+            executed = int(res["steps"].sum(dtype=torch.int64).item())
+            es["eps=%g" % eps] = {"nets_per_s": N_NETS / dt, "executed_self_applications_per_s": executed / dt,
+                                  "mean_steps": executed / N_NETS,
+                                  "classes": dict(zip(eng.CLS_NAMES, res["counters"].cpu().tolist()))}
+            del pop
+        out["early_stop"] = {"workload": "ww22_run_net_until_vergence", "nets": N_NETS, "step_limit": N_STEPS, "by_epsilon": es}
+        # configs[4]: known-fixpoint variation sweep, 100 M perturbed identity fixpoints per noise level 1e0 .. 1e-9,
         # <= 100 self-applications each; means next to the reference's logged values (100 trials per level)
         dwk = eng.make_desc(eng.KIND_WW, 2, 2)
         basefix = np.zeros(14, np.float32)
         basefix[[0, 8, 12]] = 1.0
         ref_y = [3.63, 5.02, 6.46, 8.04, 9.61, 11.23, 12.99, 14.58, 21.95, 26.45]
         ref_z = [0, 0, 0, 0, 0.04, 1.38, 3.23, 4.84, 11.91, 16.47]
-        nt, scale, ys, zs, steps_total = 1 << 24, 1.0, [], [], 0.0
+        nt, scale, ys, zs, steps_total = 100_000_000, 1.0, [], [], 0.0
         eng.kfv(dwk, basefix, nt, 1.0, 0, 100, 1e-4, seed=11, want_times=False)
         t_kfv = 0.0
         for level in range(10):
