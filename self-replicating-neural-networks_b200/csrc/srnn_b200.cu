@@ -172,17 +172,89 @@ __device__ __forceinline__ void tile_store(float *__restrict__ w, int64_t ld, in
     __syncthreads();
     tile_stage_out<NW, BS>(w, ld, base, n, tile);
 }
+// One record to / from registers by one thread (gathers and scatters by index), in the widest words its address
+// allows: H leading floats bring the address to a 16-byte boundary (one 32-bit and / or one 64-bit word), then 128-bit
+// words, then the tail.  A WW(2,2) record (56 B) moves in 4 instructions instead of 14, an AGG(4,2,2) record in 5
+// instead of 20 (pair-apply kernel, 2^24 pairs in arena order: 0.86 -> 0.46 ms).
+enum { LD_PLAIN = 0, LD_RO = 1, LD_CG = 2 };   // ordinary load / read-only path / L1-bypassing
+template <int MODE, class T>
+__device__ __forceinline__ T ld_as(const float *p) {
+    const T *q = reinterpret_cast<const T *>(p);
+    return MODE == LD_RO ? __ldg(q) : MODE == LD_CG ? __ldcg(q) : *q;
+}
+template <int NW, int H, int MODE>
+__device__ __forceinline__ void record_get_h(const float *src, float *reg) {
+    int k = 0;
+    if (H & 1) { reg[0] = ld_as<MODE, float>(src); k = 1; }
+    if (H & 2) {
+        const float2 v = ld_as<MODE, float2>(src + k);
+        reg[k] = v.x; reg[k + 1] = v.y;
+        k += 2;
+    }
+#pragma unroll
+    for (int q = 0; q < (NW - H) / 4; ++q, k += 4) {
+        const float4 v = ld_as<MODE, float4>(src + k);
+        reg[k] = v.x; reg[k + 1] = v.y; reg[k + 2] = v.z; reg[k + 3] = v.w;
+    }
+    if ((NW - H) & 2) {
+        const float2 v = ld_as<MODE, float2>(src + k);
+        reg[k] = v.x; reg[k + 1] = v.y;
+        k += 2;
+    }
+    if ((NW - H) & 1) reg[k] = ld_as<MODE, float>(src + k);
+}
+template <int NW, int H>
+__device__ __forceinline__ void record_put_h(float *dst, const float *reg) {
+    int k = 0;
+    if (H & 1) { dst[0] = reg[0]; k = 1; }
+    if (H & 2) { *reinterpret_cast<float2 *>(dst + k) = make_float2(reg[k], reg[k + 1]); k += 2; }
+#pragma unroll
+    for (int q = 0; q < (NW - H) / 4; ++q, k += 4)
+        *reinterpret_cast<float4 *>(dst + k) = make_float4(reg[k], reg[k + 1], reg[k + 2], reg[k + 3]);
+    if ((NW - H) & 2) { *reinterpret_cast<float2 *>(dst + k) = make_float2(reg[k], reg[k + 1]); k += 2; }
+    if ((NW - H) & 1) dst[k] = reg[k];
+}
+template <int NW, int MODE>
+__device__ __forceinline__ void record_get(const float *src, float *reg) {
+    static_assert(NW >= 3, "record shorter than the longest alignment head");
+    switch ((4 - (int)((reinterpret_cast<uintptr_t>(src) >> 2) & 3)) & 3) {   // floats up to the next 16-byte boundary
+    case 0: record_get_h<NW, 0, MODE>(src, reg); break;
+    case 1: record_get_h<NW, 1, MODE>(src, reg); break;
+    case 2: record_get_h<NW, 2, MODE>(src, reg); break;
+    default: record_get_h<NW, 3, MODE>(src, reg); break;
+    }
+}
+// The soup's partner gathers sit on the latency-critical path of a tile: there the four-way alignment switch costs
+// more (lanes of a warp diverge by record parity, 0.68 -> 0.88 ms per generation at 10 M particles) than the wider
+// words save.  This variant takes 64-bit words when the record is 8-byte aligned -- the same answer for every lane of a
+// packed arena with an even number of weights, so the branch is uniform -- and 32-bit words otherwise.
+template <int NW, int MODE>
+__device__ __forceinline__ void record_get_uniform(const float *src, float *reg) {
+    if (NW % 2 == 0 && (reinterpret_cast<uintptr_t>(src) & 7) == 0) {
+#pragma unroll
+        for (int k = 0; k < NW; k += 2) {
+            const float2 v = ld_as<MODE, float2>(src + k);
+            reg[k] = v.x; reg[k + 1] = v.y;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < NW; ++k) reg[k] = ld_as<MODE, float>(src + k);
+    }
+}
 template <int NW>
 __device__ __forceinline__ void record_load(const float *__restrict__ w, int64_t ld, int64_t i, float *reg) {
-    const float *src = w + i * ld;
-#pragma unroll
-    for (int k = 0; k < NW; ++k) reg[k] = __ldg(src + k);
+    record_get<NW, LD_RO>(w + i * ld, reg);
 }
 template <int NW>
 __device__ __forceinline__ void record_store(float *__restrict__ w, int64_t ld, int64_t i, const float *reg) {
+    static_assert(NW >= 3, "record shorter than the longest alignment head");
     float *dst = w + i * ld;
-#pragma unroll
-    for (int k = 0; k < NW; ++k) dst[k] = reg[k];
+    switch ((4 - (int)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3)) & 3) {
+    case 0: record_put_h<NW, 0>(dst, reg); break;
+    case 1: record_put_h<NW, 1>(dst, reg); break;
+    case 2: record_put_h<NW, 2>(dst, reg); break;
+    default: record_put_h<NW, 3>(dst, reg); break;
+    }
 }
 
 __device__ __forceinline__ void block_histogram(int cls, bool active, unsigned int *sh /*[5]*/,
@@ -287,8 +359,8 @@ __global__ void __launch_bounds__(BS) apply_kernel(const float *op_w, int64_t op
     {   // op / in may alias out (attack on self): plain loads, no read-only path
         const float *so = op_w + (op_idx ? (int64_t)op_idx[p] : p) * op_ld;
         const float *si = in_w + (in_idx ? (int64_t)in_idx[p] : p) * in_ld;
-#pragma unroll
-        for (int k = 0; k < S::NW; ++k) { op[k] = so[k]; in[k] = si[k]; }
+        record_get<S::NW, LD_PLAIN>(so, op);
+        record_get<S::NW, LD_PLAIN>(si, in);
     }
     net_apply<S>(op, in, out, opaque_one());
     record_store<S::NW>(out_w, out_ld, out_idx ? out_idx[p] : p, out);
@@ -306,18 +378,24 @@ __global__ void __launch_bounds__(BS) forward_kernel(const float *__restrict__ w
     record_load<S::NW>(w, ld, idx ? idx[p] : p, op);
     if constexpr (S::KIND == SRNN_KIND_RNN) {
         float seq[S::NW], out[S::NW];
-#pragma unroll
-        for (int t = 0; t < S::NW; ++t) seq[t] = x[p * S::NW + t];
+        record_get<S::NW, LD_RO>(x + p * S::NW, seq);
         rnn_forward_seq<S, false>(op, seq, out, nullptr);
-#pragma unroll
-        for (int t = 0; t < S::NW; ++t) y[p * S::NW + t] = out[t];
+        record_store<S::NW>(y, S::NW, p, out);
     } else {
         float in[S::IO], out[S::OUTW];
+        if constexpr (S::IO >= 3) {
+            record_get<S::IO, LD_RO>(x + p * S::IO, in);
+        } else {
 #pragma unroll
-        for (int q = 0; q < S::IO; ++q) in[q] = x[p * S::IO + q];
+            for (int q = 0; q < S::IO; ++q) in[q] = __ldg(x + p * S::IO + q);
+        }
         mlp_forward<S>(op, in, out);
+        if constexpr (S::OUTW >= 3) {
+            record_store<S::OUTW>(y, S::OUTW, p, out);
+        } else {
 #pragma unroll
-        for (int q = 0; q < S::OUTW; ++q) y[p * S::OUTW + q] = out[q];
+            for (int q = 0; q < S::OUTW; ++q) y[p * S::OUTW + q] = out[q];
+        }
     }
 }
 
@@ -402,9 +480,10 @@ __global__ void __launch_bounds__(BS) train_kernel(float *__restrict__ w, int64_
     __syncthreads();  // codes visible
     if (active) {
         if (teacher_w) {
-            const float *src = teacher_w + (teacher_idx ? (int64_t)teacher_idx[i] : i) * teacher_ld;
+            float tch[S::NW];   // teacher may be the arena being trained (learn_from inside one population): plain loads
+            record_get<S::NW, LD_PLAIN>(teacher_w + (teacher_idx ? (int64_t)teacher_idx[i] : i) * teacher_ld, tch);
 #pragma unroll
-            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = src[k];
+            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tch[k];
         }
         double loss = 0.0;
         const bool ordered = S::NS > 1 && perm_mode != SRNN_PERM_NONE;
@@ -812,8 +891,9 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
             if (prefetch && qa < QCAP) {
                 const int32_t nx = CG ? __ldcg(next + my_head[r]) : __ldg(next + my_head[r]);
                 const float *rec = shard_record(snap, snap_ld, my_head[r]);
-#pragma unroll
-                for (int k = 0; k < NW; ++k) att_s[qa * NW + k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
+                float tmp[NW];
+                record_get_uniform<NW, CG ? LD_CG : LD_RO>(rec, tmp);
+                tile_put<NW>(att_s, qa, tmp);
                 single_s[qa] = nx < 0;
             }
         }
@@ -822,8 +902,9 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
             queue_l[ql] = (uint16_t)v;
             if (prefetch && ql < QCAP) {
                 const float *rec = shard_record(snap, snap_ld, lr[r]);
-#pragma unroll
-                for (int k = 0; k < NW; ++k) tch_s[ql * NW + k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
+                float tmp[NW];
+                record_get_uniform<NW, CG ? LD_CG : LD_RO>(rec, tmp);
+                tile_put<NW>(tch_s, ql, tmp);
             }
         }
     }
@@ -853,9 +934,10 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
 #pragma unroll
             for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = tch_s[q * NW + k];
         } else {
-            const float *rec = shard_record(snap, snap_ld, lrn_s[v]);
+            float tmp[NW];
+            record_get_uniform<NW, CG ? LD_CG : LD_RO>(shard_record(snap, snap_ld, lrn_s[v]), tmp);
 #pragma unroll
-            for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = CG ? __ldcg(rec + k) : __ldg(rec + k);
+            for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = tmp[k];
         }
         for (int e = 0; e < sev; ++e) {
             if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + base + v), ep + (uint64_t)e, sc.ord, sc.stride);
@@ -1080,9 +1162,7 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
             if (a > last) { ++larger; if (a < best) best = a; }
         if (larger == 0) break;
         float op[S::NW], res[S::NW];
-        const float *rec = shard_record(snap, snap_ld, best);
-#pragma unroll
-        for (int k = 0; k < S::NW; ++k) op[k] = CG ? __ldcg(rec + k) : __ldg(rec + k);
+        record_get_uniform<S::NW, CG ? LD_CG : LD_RO>(shard_record(snap, snap_ld, best), op);
         net_apply<S>(op, cur, res, opaque_one());
 #pragma unroll
         for (int k = 0; k < S::NW; ++k) cur[k] = res[k];
