@@ -208,6 +208,23 @@ SRNN_DEV void ww_apply(const float *op, const float *in, float *out, float one) 
         mlp_forward<S>(op, x, &out[k]);
     });
 }
+// a / N for a compile-time count N, correctly rounded like __ddiv_rn(a, N) but in three instructions instead of the
+// ~20 of the general division: with y = rn(1/N) and q0 = rn(a*y) (within one ulp of a/N), the remainder
+// r = a - N*q0 is exact in one FMA and rn(q0 + r*y) is the correctly rounded quotient (Markstein).  The operands here
+// are sums of float32 values, far from the double range limits; an infinite sum stays infinite, NaN stays NaN, and
+// the sums are never -0.  Checked against IEEE division for N = 1..64 on 1.3e9 operands (DESIGN.md "Kernels").
+template <int N>
+SRNN_DEV double div_count(double a) {
+    if constexpr ((N & (N - 1)) == 0) {
+        return __dmul_rn(a, 1.0 / (double)N);   // power of two: exact
+    } else {
+        constexpr double y = 1.0 / (double)N;
+        const double q0 = __dmul_rn(a, y);
+        const double r = __fma_rn(-(double)N, q0, a);
+        const double q = __fma_rn(r, y, q0);
+        return isinf(q0) ? q0 : q;
+    }
+}
 // AggregatingNeuralNetwork.apply_to_weights, code/network.py:359-386 (aggregate_average :294-301, R5)
 template <class S>
 SRNN_DEV void agg_means(const float *in, float *agg) {
@@ -217,7 +234,7 @@ SRNN_DEV void agg_means(const float *in, float *agg) {
         double tot = 0.0;
 #pragma unroll
         for (int k = lo; k < hi; ++k) tot = __dadd_rn(tot, (double)in[k]);
-        agg[g] = (float)__ddiv_rn(tot, (double)(hi - lo));
+        agg[g] = (float)div_count<hi - lo>(tot);
     });
 }
 template <class S>
@@ -566,7 +583,7 @@ SRNN_DEV double train_epoch(float *w, const SgdScratch &sc, bool ordered, float 
             const float l = mlp_sgd_sample<S>(w, x, &v, lr, sc.one);
             if (want_loss) acc = __dadd_rn(acc, (double)l);   // only the last epoch's loss is ever reported
         }
-        return __ddiv_rn(acc, (double)S::NW);
+        return div_count<S::NW>(acc);
     } else if constexpr (S::KIND == SRNN_KIND_AGG) {  // compute_samples, code/network.py:414-417
         float t[S::NW], agg[S::AGGS];
 #pragma unroll
