@@ -457,6 +457,34 @@ def test_nan_inf_are_states_not_errors(eng):
     assert (cls[[0, 1, 2, 10, 11, 12]] == 0).all()
 
 
+@pytest.mark.parametrize("key", [(1, 2, 2, 4), (1, 2, 2, 3), (1, 3, 2, 4)])
+def test_agg_block_means_exact_division(eng, key):
+    """The AGG block mean divides a float64 sum by a compile-time count with a three-instruction correctly rounded
+    quotient (div_count); the oracle uses the IEEE division.  Victims with wildly mixed exponents, cancellation, huge
+    and tiny magnitudes, infinities and NaNs must come out bit-identical (counts 5, 6+, 3: non powers of two)."""
+    dg, do = both(eng, key)
+    nw = dg.n_weights
+    n = 1 << 16
+    rng = np.random.default_rng(17)
+    bits = rng.integers(0, 2 ** 32, (n, nw), dtype=np.uint64).astype(np.uint32)
+    w = bits.view(np.float32).copy()                      # every exponent, both signs, NaNs, infinities
+    w[np.abs(w) < np.float32(1.1754944e-38)] = 0.0        # no denormals: stored weights are always flushed results (R1)
+    w[: n // 4] = (rng.standard_normal((n // 4, nw)) * 10.0 ** rng.integers(-30, 30, (n // 4, 1))).astype(np.float32)
+    w[n // 4: n // 2] = glorot_population(key, n // 4, seed=3)
+    w[n // 2, :] = np.float32(3.4028235e38)              # the sum leaves the float32 range, the mean returns to it
+    w[n // 2 + 1, :] = np.float32(1.1754944e-38)
+    w[n // 2 + 2, :] = 0.0
+    w[n // 2 + 3, :] = -0.0
+    ops = glorot_population(key, n, seed=4)               # finite operators: the result shows the means, not just NaN
+    pop_op, pop_in, pop_out = (eng.Population.from_numpy(dg, a) for a in (ops, w, np.zeros_like(w)))
+    pop_op.apply_pairs(None, pop_in, None, pop_out, None, n=n)
+    ref = np.zeros_like(w)
+    ar = np.arange(n)
+    oracle.apply(do, ops, ar, w, ar, ref, ar, n)
+    assert_same_weights(pop_out.numpy(), ref, "agg means")
+    assert np.isfinite(ref).all(axis=1).sum() > n // 2
+
+
 # ---------------------------------------------------------------- generic run-time-shape path
 GENERIC_SHAPES = [(0, 4, 3, 0), (0, 1, 1, 0), (0, 5, 2, 0), (1, 3, 3, 5), (1, 4, 1, 2), (2, 3, 2, 0), (2, 1, 3, 0)]
 
