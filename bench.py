@@ -193,7 +193,7 @@ def _timed(torch, fn, reps=1):
 def secondary_legs(eng, torch, dist, rank, world, dev):
     """The other half of BASELINE.json's metric (soup generations/s) and the self-training config, device-timed.
     Reported as extra keys of the JSON line; the headline `value` stays net self-applications/s."""
-    from soup import PopulationSoup
+    from soup import PopulationSoup, evolve_together
     out = {}
 
     def sync_max(x):
@@ -316,14 +316,20 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
         # sharded by particle index over the ranks with one all-gather of the record arena per generation
         third = (10_000_000 // 3) // world * world
         kw = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, epsilon=1e-4)
-        gens, res = 20, {}
+        gens, res, host = 20, {}, {}
         for exchange in ("allgather", "auto"):
             soups = [PopulationSoup(k, third, aggregates=a, seed=5 + k, exchange=exchange, **kw).seed_particles()
                      for k, a in ((eng.KIND_WW, 0), (eng.KIND_AGG, 4), (eng.KIND_RNN, 0))]
             for s in soups:
                 s.evolve(2)
             dist.barrier()
-            res[soups[0].exchange] = sync_max(_timed(torch, lambda: [s.evolve(1) for s in soups], reps=gens))
+            res[soups[0].exchange] = sync_max(_timed(torch, lambda: evolve_together(soups, gens)) / gens)
+            # host time to ENQUEUE a generation (no device sync): shows whether the loop is launch-bound at this N
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            evolve_together(soups, gens)
+            host[soups[0].exchange] = sync_max((time.perf_counter() - t0) / gens)
+            torch.cuda.synchronize()
             gathered = sum(s.size * s.desc.n_weights * 4 for s in soups)
             del soups
             torch.cuda.empty_cache()
@@ -332,6 +338,7 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
                        "config": dict(workload="mixed_soup_10m_sharded", particles=3 * third, kinds="WW/AGG/RNN thirds",
                                       ranks=world, generations=gens, exchange=best, **kw),
                        "generations_per_s_by_exchange": {k: 1.0 / v for k, v in res.items()},
+                       "host_enqueue_ms_per_generation": {k: v * 1e3 for k, v in host.items()},
                        "allgather_bytes_per_generation_per_gpu": gathered}
     return out
 

@@ -53,6 +53,32 @@ class OracleBackend:
         n_dead[0] = int(d.sum())
 
 
+def run_together(args, rank, world):
+    """A mixed soup: the three kinds advance in lock step, one cross-GPU barrier per generation."""
+    from soup import PopulationSoup, evolve_together
+    kw = dict(attacking_rate=0.3, learn_from_rate=0.2, train=1, learn_from_severity=2, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4)
+    soups = [PopulationSoup(k, args.size, aggregates=4 if k == 1 else 0, seed=31, exchange=args.exchange, **kw)
+             for k in (0, 1, 2)]
+    for ps in soups:
+        ps.track_uids = True
+        ps.seed_particles()
+    evolve_together(soups, args.gens)
+    out = dict(world=world, exchange=soups[0].exchange)
+    for k, ps in enumerate(soups):
+        counts = ps.count()
+        full = torch.zeros((ps.size, ps.desc.n_weights), dtype=torch.float32, device=ps.w.device)
+        uids = torch.zeros(ps.size, dtype=torch.int64, device=ps.w.device)
+        dist.all_gather_into_tensor(full, ps.w.contiguous())
+        dist.all_gather_into_tensor(uids, ps.uid)
+        out.update({"w%d" % k: full.cpu().numpy(), "uid%d" % k: uids.cpu().numpy(),
+                    "counts%d" % k: np.array(list(counts.values())), "next_uid%d" % k: ps.next_uid, "time%d" % k: ps.time})
+    if rank == 0:
+        np.savez(args.out, **out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--backend", required=True)
@@ -61,6 +87,7 @@ def main():
     ap.add_argument("--size", type=int, default=4096)
     ap.add_argument("--gens", type=int, default=4)
     ap.add_argument("--exchange", default="auto")
+    ap.add_argument("--together", type=int, default=0, help="1: all three kinds in lock step (soup.evolve_together)")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     if args.backend == "nccl":
@@ -69,6 +96,9 @@ def main():
     else:
         dist.init_process_group("gloo")
     from soup import PopulationSoup
+    if args.together:
+        run_together(args, rank, world)
+        return
     ps = PopulationSoup(args.kind, args.size, aggregates=4 if args.kind == 1 else 0, seed=31,
                         backend=OracleBackend() if args.backend == "gloo" else None, exchange=args.exchange,
                         attacking_rate=0.3,

@@ -33,13 +33,13 @@ def _reference(kind, size, gens):
     return w, uid, next_uid, oracle.classify(do, w, 1e-4)[1]
 
 
-def _run(backend, world, kind, size, gens, tmp_path, exchange="auto"):
-    out = str(tmp_path / ("soup_%s_%d_%s.npz" % (backend, kind, exchange)))
+def _run(backend, world, kind, size, gens, tmp_path, exchange="auto", together=0):
+    out = str(tmp_path / ("soup_%s_%d_%s_%d.npz" % (backend, kind, exchange, together)))
     port = 29500 + (os.getpid() + kind * 7) % 2000
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "dist_soup_worker.py"),
            "--backend", backend, "--out", out, "--kind", str(kind), "--size", str(size), "--gens", str(gens),
-           "--exchange", exchange]
+           "--exchange", exchange, "--together", str(together)]
     env = dict(os.environ, OMP_NUM_THREADS="2")
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
@@ -81,3 +81,34 @@ def test_two_ranks_nccl_equals_one(kind, exchange, tmp_path):
     got = _run("nccl", 2, kind, 8192, 3, tmp_path, exchange)
     assert int(got["world"]) == 2 and str(got["exchange"]) == exchange
     _check(got, kind, 8192, 3)
+
+
+@pytest.mark.gpu
+def test_mixed_soup_in_lock_step_nccl(tmp_path):
+    """soup.evolve_together: the three kinds of a mixed sharded soup on separate streams with one cross-GPU barrier
+    per generation -- every kind still equals its single-owner oracle run bit for bit (weights, uids, counts)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    got = _run("nccl", 2, 0, 8192, 3, tmp_path, "peer", together=1)
+    assert int(got["world"]) == 2 and str(got["exchange"]) == "peer"
+    for kind in (0, 1, 2):
+        sub = {k: got["%s%d" % (k, kind)] for k in ("w", "uid", "counts", "next_uid")}
+        assert int(got["time%d" % kind]) == 3
+        _check(sub, kind, 8192, 3)
+
+
+@pytest.mark.gpu
+def test_evolve_together_single_gpu_falls_back(tmp_path):
+    """Unsharded soups take the plain loop: same result as evolving each soup on its own."""
+    import torch
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE), "self-replicating-neural-networks_b200"))
+    from soup import PopulationSoup, evolve_together
+    kw = dict(attacking_rate=0.3, learn_from_rate=0.2, train=1, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+    a = [PopulationSoup(k, 4096, aggregates=4 if k == 1 else 0, seed=9, **kw).seed_particles() for k in (0, 1, 2)]
+    b = [PopulationSoup(k, 4096, aggregates=4 if k == 1 else 0, seed=9, **kw).seed_particles() for k in (0, 1, 2)]
+    evolve_together(a, 3)
+    for s in b:
+        s.evolve(3)
+    for x, y in zip(a, b):
+        assert x.time == y.time == 3 and torch.equal(x.w.view(torch.int32), y.w.view(torch.int32))
