@@ -234,9 +234,10 @@ class _CudaBackend:
                        action=action, dead=dead)
 
     def soup_sync_peers(self, desc, sp_kwargs, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action,
-                        dead):
-        _eng.soup_sync_peers(desc, _eng.make_soup_params(**sp_kwargs), shard_ptrs, shard_len, my_shard, ld, w_out, seed,
-                             gen, scratch, action=action, dead=dead)
+                        dead, stream=None):
+        sp = sp_kwargs if isinstance(sp_kwargs, _eng.SoupParams) else _eng.make_soup_params(**sp_kwargs)
+        _eng.soup_sync_peers(desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action=action,
+                             dead=dead, stream=stream)
 
     def peer_arena(self, n_local, nw, group):
         """Two ping-pong arenas in NVLink-mapped symmetric memory: returns (tensor (2, n_local, nw), handle) or None
@@ -304,18 +305,18 @@ def evolve_together(soups, iterations=1):
     dev = soups[0].w.device
     side = _SIDE_STREAMS.setdefault((dev.index, len(soups)), [torch.cuda.Stream(device=dev) for _ in soups])
     main = torch.cuda.current_stream(dev)
-    sps = [s._sp() for s in soups]
+    sps = [_eng.make_soup_params(**s._sp()) if isinstance(s.backend, _CudaBackend) else s._sp() for s in soups]
     fork, joins = torch.cuda.Event(), [torch.cuda.Event() for _ in soups]
+    barrier = soups[0]._peer[1].barrier
     for _ in range(iterations):
         fork.record(main)
         for s, sp, st, ev in zip(soups, sps, side, joins):
             s.time += 1
             st.wait_event(fork)
-            with torch.cuda.stream(st):
-                s._peer_generation(sp)
+            s._peer_generation(sp, stream=st)
             ev.record(st)
             main.wait_event(ev)
-        soups[0]._peer[1].barrier()       # one barrier orders every kind's reads of generation g on every rank
+        barrier()                         # one barrier orders every kind's reads of generation g on every rank
         for s in soups:
             s._peer_flip()
     return soups
@@ -361,6 +362,7 @@ class PopulationSoup:
             if self._peer is None and exchange == "peer":
                 raise RuntimeError("peer-memory exchange requested but symmetric memory is unavailable")
         self.exchange = "peer" if self._peer is not None else ("allgather" if self.world > 1 else "none")
+        self._shard_arrays = None
         if self._peer is not None:
             buf, _ = self._peer
             self._cur = 0
@@ -439,13 +441,15 @@ class PopulationSoup:
             self._log_watched()
         return self
 
-    def _peer_generation(self, sp):
-        """Launch generation self.time of a peer-exchange soup on the current stream (no cross-GPU barrier)."""
-        buf, hdl = self._peer
-        stride = self.n_local * self.desc.n_weights * 4
-        shards = [int(q) + self._cur * stride for q in hdl.buffer_ptrs]
-        self.backend.soup_sync_peers(self.desc, sp, shards, self.n_local, self.rank, self.desc.n_weights, self._next,
-                                     self.seed, self.time, self._scratch, self.action, self.dead)
+    def _peer_generation(self, sp, stream=None):
+        """Launch generation self.time of a peer-exchange soup (no cross-GPU barrier) on `stream` / the current stream."""
+        if self._shard_arrays is None:      # the peers' two ping-pong arenas, as ready-made pointer tables
+            stride = self.n_local * self.desc.n_weights * 4
+            self._shard_arrays = [_eng.shard_ptr_array([int(q) + c * stride for q in self._peer[1].buffer_ptrs])
+                                  for c in (0, 1)]
+        self.backend.soup_sync_peers(self.desc, sp, self._shard_arrays[self._cur], self.n_local, self.rank,
+                                     self.desc.n_weights, self._next, self.seed, self.time, self._scratch, self.action,
+                                     self.dead, stream=stream)
 
     def _peer_flip(self):
         self._cur ^= 1

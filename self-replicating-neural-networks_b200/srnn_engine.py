@@ -297,14 +297,19 @@ def soup_exact(desc, params, w, seed, gen, scratch, att=None, lrn=None, action=N
 
 
 def soup_sync_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action=None, loss=None,
-                    dead=None):
+                    dead=None, stream=None):
     """One generation of a sharded soup reading partner records straight from the peers' arenas (shard_ptrs = device
-    pointers, as ints, of every rank's start-of-generation arena mapped into this process)."""
-    arr = (C.c_void_p * len(shard_ptrs))(*[C.c_void_p(int(q)) for q in shard_ptrs])
-    _chk(lib().srnn_soup_sync_peers(C.byref(desc), C.byref(params), arr, C.c_int32(len(shard_ptrs)), C.c_int64(shard_len),
+    pointers, as ints or a ready ctypes array of void pointers, of every rank's start-of-generation arena mapped into
+    this process).  stream: a torch.cuda.Stream to launch on (default: the current stream)."""
+    arr = shard_ptrs if isinstance(shard_ptrs, C.Array) else shard_ptr_array(shard_ptrs)
+    _chk(lib().srnn_soup_sync_peers(C.byref(desc), C.byref(params), arr, C.c_int32(len(arr)), C.c_int64(shard_len),
                                     C.c_int32(my_shard), C.c_int64(ld), _ptr(w_out), C.c_int64(w_out.shape[1]),
                                     C.c_uint64(seed), C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead),
-                                    _stream()))
+                                    _stream() if stream is None else C.c_void_p(stream.cuda_stream)))
+
+
+def shard_ptr_array(shard_ptrs):
+    return (C.c_void_p * len(shard_ptrs))(*[C.c_void_p(int(q)) for q in shard_ptrs])
 
 
 def soup_sync_run(desc, params, w_a, w_b, seed, gen0, n_gens, scratch, action=None, dead=None):
