@@ -365,7 +365,11 @@ def main():
     import srnn_engine as eng
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    host_cpus = None
     if world > 1:
+        # one process per GPU: stay on the GPU's NUMA node so the pinned staging buffers of the e2e leg are local to it
+        # (N = 1 keeps every core: the cpu_baseline leg uses them all)
+        host_cpus = eng.bind_host_thread_to_gpu(local_rank)
         dist.init_process_group("nccl", device_id=dev)
     n = args.nets
     K, W = args.steps, args.warmup
@@ -461,7 +465,8 @@ def main():
             "config": {"workload": "ww22_self_application", "nets_per_gpu": n, "self_applications_per_net": N_STEPS,
                        "net": "WeightwiseNeuralNetwork(width=2, depth=2)", "init": "glorot_uniform (Philox)",
                        "fresh_arenas": R, "l2": "inputs larger than L2 (0.94 GB arena per step, new arena each step)",
-                       "parallelism": "population sharded by net index, no data-path collective"},
+                       "parallelism": "population sharded by net index, no data-path collective",
+                       "host_affinity": ("GPU-local NUMA node, %d cpus" % len(host_cpus)) if host_cpus else "unbound"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": 40},
             "gpu_launches": K,

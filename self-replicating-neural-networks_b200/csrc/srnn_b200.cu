@@ -132,27 +132,49 @@ __device__ __forceinline__ void tile_put(float *tile, int r, const float *reg) {
 // NT threads stage TILE consecutive records (TILE a multiple of NT)
 template <int NW, int NT, bool CG = false, int TILE = NT>
 __device__ __forceinline__ void tile_stage_in(const float *__restrict__ w, int64_t ld, int64_t base, int64_t n, float *tile) {
-    const int cnt = (int)max((int64_t)0, min((int64_t)TILE, n - base));
-    if (ld == NW) {
-        flat_copy<NT, CG>(tile, w + base * NW, cnt * NW);
-    } else {
-        for (int v = threadIdx.x; v < cnt; v += NT) {
-            const float *src = w + (base + v) * ld;
+    if constexpr (TILE == NT) {   // one record per thread: kept apart, the general form below costs registers
+        const int cnt = (int)min((int64_t)NT, n - base);   // (RNN train kernel 127 -> 144, 7 % slower)
+        if (ld == NW) {
+            flat_copy<NT, CG>(tile, w + base * NW, cnt * NW);
+        } else if ((int)threadIdx.x < cnt) {
+            const float *src = w + (base + threadIdx.x) * ld;
 #pragma unroll
-            for (int k = 0; k < NW; ++k) tile[v * NW + k] = CG ? __ldcg(src + k) : __ldg(src + k);
+            for (int k = 0; k < NW; ++k) tile[threadIdx.x * NW + k] = CG ? __ldcg(src + k) : __ldg(src + k);
+        }
+    } else {
+        const int cnt = (int)max((int64_t)0, min((int64_t)TILE, n - base));
+        if (ld == NW) {
+            flat_copy<NT, CG>(tile, w + base * NW, cnt * NW);
+        } else {
+            for (int v = threadIdx.x; v < cnt; v += NT) {
+                const float *src = w + (base + v) * ld;
+#pragma unroll
+                for (int k = 0; k < NW; ++k) tile[v * NW + k] = CG ? __ldcg(src + k) : __ldg(src + k);
+            }
         }
     }
 }
 template <int NW, int NT, int TILE = NT>
 __device__ __forceinline__ void tile_stage_out(float *__restrict__ w, int64_t ld, int64_t base, int64_t n, const float *tile) {
-    const int cnt = (int)max((int64_t)0, min((int64_t)TILE, n - base));
-    if (ld == NW) {
-        flat_copy<NT>(w + base * NW, tile, cnt * NW);
-    } else {
-        for (int v = threadIdx.x; v < cnt; v += NT) {
-            float *dst = w + (base + v) * ld;
+    if constexpr (TILE == NT) {
+        const int cnt = (int)min((int64_t)NT, n - base);
+        if (ld == NW) {
+            flat_copy<NT>(w + base * NW, tile, cnt * NW);
+        } else if ((int)threadIdx.x < cnt) {
+            float *dst = w + (base + threadIdx.x) * ld;
 #pragma unroll
-            for (int k = 0; k < NW; ++k) dst[k] = tile[v * NW + k];
+            for (int k = 0; k < NW; ++k) dst[k] = tile[threadIdx.x * NW + k];
+        }
+    } else {
+        const int cnt = (int)max((int64_t)0, min((int64_t)TILE, n - base));
+        if (ld == NW) {
+            flat_copy<NT>(w + base * NW, tile, cnt * NW);
+        } else {
+            for (int v = threadIdx.x; v < cnt; v += NT) {
+                float *dst = w + (base + v) * ld;
+#pragma unroll
+                for (int k = 0; k < NW; ++k) dst[k] = tile[v * NW + k];
+            }
         }
     }
 }
@@ -245,6 +267,14 @@ template <int NW>
 __device__ __forceinline__ void record_load(const float *__restrict__ w, int64_t ld, int64_t i, float *reg) {
     record_get<NW, LD_RO>(w + i * ld, reg);
 }
+// 32-bit words only: for stores inside hot loops that are usually skipped (trajectory logging), where the alignment
+// switch of record_store would cost the loop registers (general self-apply kernel: 60 -> 72)
+template <int NW>
+__device__ __forceinline__ void record_store_scalar(float *__restrict__ w, int64_t ld, int64_t i, const float *reg) {
+    float *dst = w + i * ld;
+#pragma unroll
+    for (int k = 0; k < NW; ++k) dst[k] = reg[k];
+}
 template <int NW>
 __device__ __forceinline__ void record_store(float *__restrict__ w, int64_t ld, int64_t i, const float *reg) {
     static_assert(NW >= 3, "record shorter than the longest alignment head");
@@ -334,7 +364,7 @@ __global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restric
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
             ++it;
-            if (traj) record_store<S::NW>(traj + (int64_t)(it - 1) * n * ld, ld, i, cur);
+            if (traj) record_store_scalar<S::NW>(traj + (int64_t)(it - 1) * n * ld, ld, i, cur);
             net_apply<S>(cur, cur, nxt, opaque_one());
         }
         if (steps_out) steps_out[i] = it;
@@ -480,10 +510,11 @@ __global__ void __launch_bounds__(BS) train_kernel(float *__restrict__ w, int64_
     __syncthreads();  // codes visible
     if (active) {
         if (teacher_w) {
-            float tch[S::NW];   // teacher may be the arena being trained (learn_from inside one population): plain loads
-            record_get<S::NW, LD_PLAIN>(teacher_w + (teacher_idx ? (int64_t)teacher_idx[i] : i) * teacher_ld, tch);
+            // scalar on purpose: the wide-word variants cost registers here (RNN: 127 -> 144) and gain nothing, the
+            // epoch that follows dominates.  Plain loads: the teacher may live in the arena being trained.
+            const float *src = teacher_w + (teacher_idx ? (int64_t)teacher_idx[i] : i) * teacher_ld;
 #pragma unroll
-            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tch[k];
+            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = src[k];
         }
         double loss = 0.0;
         const bool ordered = S::NS > 1 && perm_mode != SRNN_PERM_NONE;

@@ -308,6 +308,22 @@ def soup_sync_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, se
                                     _stream() if stream is None else C.c_void_p(stream.cuda_stream)))
 
 
+def bind_host_thread_to_gpu(device_index=None):
+    """Pin the calling thread (and the pinned host buffers it allocates afterwards: first touch) to the CPUs of the
+    NUMA node the GPU hangs off.  One process per GPU on a multi-socket host otherwise stages its host->device copies
+    through the other socket.  Returns the CPU set now in force, or None when NVML cannot tell (nothing is changed)."""
+    torch = _torch()
+    try:
+        import pynvml
+        idx = torch.cuda.current_device() if device_index is None else int(device_index)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(idx).uuid))
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return sorted(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def shard_ptr_array(shard_ptrs):
     return (C.c_void_p * len(shard_ptrs))(*[C.c_void_p(int(q)) for q in shard_ptrs])
 
