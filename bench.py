@@ -234,10 +234,10 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
         out["soup_10m"] = {"metric": "soup generations/sec", "value": 20 / dt, "unit": "generations/s",
                            "config": dict(workload="soup_10m_ww_train0", particles=10_000_000, generations=20, **kw0),
                            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                        "traffic": 1.645e9, "peak_source": peak_src, "kernel": "soup_sync_kernel<WW(2,2)>",
+                                        "traffic": 1.559e9, "peak_source": peak_src, "kernel": "soup_sync_kernel<WW(2,2)>",
                                         "algorithmic_bytes": "130 B per particle-generation (112 B own record in/out + 0.2 x 56 B "
                                                              "partner records + list heads)",
-                                        "traffic_source": "ncu dram bytes of one launch at 10 M particles (1.05 GB read + 0.59 GB write)"}}
+                                        "traffic_source": "ncu dram bytes of one launch at 10 M particles (1.01 GB read + 0.55 GB write), profiles/r01_soup_sync_10m_ncu.txt"}}
         del s
         # configs[2] variant of soup_trajectorys.py:22-24: 30 self-train epochs per particle and generation
         kw30 = dict(attacking_rate=0.1, learn_from_rate=-1, train=30, remove_divergent=True, remove_zero=True, epsilon=1e-4)
