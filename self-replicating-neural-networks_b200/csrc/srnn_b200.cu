@@ -38,7 +38,10 @@ constexpr int SOUP_BS = SRNN_SOUP_BS;
 // selectable (engine_path = 2): it measured 0.91 / 1.33 ms against 0.73 / 1.18 ms for the fused kernel at 10 M particles.
 constexpr int64_t SOUP_MULTIPASS_MIN = INT64_MAX;
 // srnn_soup_sync_run chains generations (one launch each) up to this population size
-constexpr int64_t SOUP_CHAIN_MAX = 1 << 21;
+#ifndef SRNN_SOUP_CHAIN_MAX
+#define SRNN_SOUP_CHAIN_MAX (1 << 21)
+#endif
+constexpr int64_t SOUP_CHAIN_MAX = SRNN_SOUP_CHAIN_MAX;
 // largest unsharded soup the opt-in persistent cooperative variant of srnn_soup_sync_run accepts
 constexpr int64_t SOUP_PERSISTENT_MAX = 1 << 20;
 
@@ -90,6 +93,43 @@ __device__ __forceinline__ void flat_copy(float *__restrict__ dst, const float *
         for (int e = (nv << 2) + tid; e < total; e += NT) dst[e] = CG ? __ldcg(src + e) : src[e];
     } else {
         for (int e = tid; e < total; e += NT) dst[e] = CG ? __ldcg(src + e) : src[e];
+    }
+}
+// Asynchronous global -> shared copies (LDGSTS): no staging registers, and the issuing thread carries on -- the soup
+// tile kernel computes its pairing draws while its records are in flight.  Completion: async_copy_wait() + barrier.
+__device__ __forceinline__ void async_copy16(float *dst_smem, const float *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void async_copy8(float *dst_smem, const float *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void async_copy4(float *dst_smem, const float *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void async_copy_wait() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+// flat_copy's asynchronous twin for a packed arena (caller checked ld == NW); dst is 16-byte aligned shared memory
+template <int NT>
+__device__ __forceinline__ void flat_copy_async(float *dst, const float *__restrict__ src, int total) {
+    const int tid = threadIdx.x;
+    if (((uintptr_t)src & 15) == 0) {
+        const int nv = total >> 2;
+        for (int e = tid; e < nv; e += NT) async_copy16(dst + 4 * e, src + 4 * e);
+        for (int e = (nv << 2) + tid; e < total; e += NT) async_copy4(dst + e, src + e);
+    } else {
+        for (int e = tid; e < total; e += NT) async_copy4(dst + e, src + e);
+    }
+}
+// one record global -> shared, asynchronously, in 64-bit words when its address allows (else 32-bit)
+template <int NW>
+__device__ __forceinline__ void record_copy_async(float *dst_smem, const float *src) {
+    if (NW % 2 == 0 && (reinterpret_cast<uintptr_t>(src) & 7) == 0) {
+#pragma unroll
+        for (int k = 0; k < NW; k += 2) async_copy8(dst_smem + k, src + k);
+    } else {
+#pragma unroll
+        for (int k = 0; k < NW; ++k) async_copy4(dst_smem + k, src + k);
     }
 }
 template <int NW>
@@ -857,6 +897,9 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 #ifndef SRNN_SOUP_PPT
 #define SRNN_SOUP_PPT 2
 #endif
+#ifndef SRNN_SOUP_ASYNC
+#define SRNN_SOUP_ASYNC 1   // cp.async staging of the tile and the partner records (0: through registers)
+#endif
 // shared memory of one CTA: tile + two partner-prefetch areas (TILE/4 records each) + queues (static) and the
 // per-thread SGD scratch (dynamic); shapes whose records are too large for 48 KB keep one particle per thread
 __host__ __device__ constexpr int soup_static_smem(int nw, int ppt) { return nw * 4 * SOUP_BS * ppt * 3 / 2 + 9 * SOUP_BS * ppt + 64; }
@@ -889,8 +932,13 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     const uint64_t ep = gen * (uint64_t)(sev + tr);
     const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
     SgdScratch sc = sgd_scratch<S>(smem, SBS);
-    // ---- everything that only needs the particle index is issued up front so the DRAM latencies overlap:
-    //      the list heads, the tile staging, the pairing draws
+    // ---- everything that only needs the particle index is issued up front so the DRAM latencies overlap: the list
+    //      heads, the tile itself (asynchronous copies: the thread goes on to its pairing draws while the records are in
+    //      flight) and -- known as soon as the draw is -- the teacher's record of every learner
+    const bool prefetch = tr == 0;
+    constexpr bool ASYNC = !CG && SRNN_SOUP_ASYNC;   // the persistent kernel must bypass L1: it keeps the register path
+    if (tid == 0) { q_len = 0; ql_len = 0; }
+    if (ASYNC) __syncthreads();   // nothing is in flight yet: this barrier is free, and the queues can fill below
     int32_t my_head[PPT];
     int64_t at[PPT], lr[PPT];
 #pragma unroll
@@ -898,21 +946,30 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
         const int64_t i = base + tid + r * SBS;
         my_head[r] = i < n ? (CG ? __ldcg(head + i) : __ldg(head + i)) : -1;
     }
-    tile_stage_in<NW, SBS, CG, TILE>(own, snap_ld, base, n, tile);
-    if (tid == 0) { q_len = 0; ql_len = 0; }
+    if (ASYNC && snap_ld == NW) {
+        flat_copy_async<SBS>(tile, own + base * NW, (int)max((int64_t)0, min((int64_t)TILE, n - base)) * NW);
+    } else {
+        tile_stage_in<NW, SBS, CG, TILE>(own, snap_ld, base, n, tile);
+    }
 #pragma unroll
     for (int r = 0; r < PPT; ++r) {
-        const int64_t i = base + tid + r * SBS;
+        const int v = tid + r * SBS;
+        const int64_t i = base + v;
         at[r] = -1; lr[r] = -1;
         if (i < n) soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at[r], &lr[r]);
-        lrn_s[tid + r * SBS] = (int32_t)lr[r];
+        lrn_s[v] = (int32_t)lr[r];
+        if (ASYNC && lr[r] >= 0 && sev > 0) {
+            const int ql = atomicAdd(&ql_len, 1);
+            queue_l[ql] = (uint16_t)v;
+            if (prefetch && ql < QCAP) record_copy_async<NW>(tch_s + ql * NW, shard_record(snap, snap_ld, lr[r]));
+        }
     }
+    if (ASYNC) async_copy_wait();
     __syncthreads();
     // ---- owners enqueue their events and, in the memory-latency-bound regime (no self-training in the generation),
     //      PREFETCH the partner records into shared memory: one DRAM round trip for attackers and teachers together
     //      instead of one per serial phase (-9 % at 10 M particles; with training the extra instructions cost more
     //      than the latency they hide, so there the partners are fetched inside the phases)
-    const bool prefetch = tr == 0;
 #pragma unroll
     for (int r = 0; r < PPT; ++r) {
         const int v = tid + r * SBS;
@@ -922,23 +979,27 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
             if (prefetch && qa < QCAP) {
                 const int32_t nx = CG ? __ldcg(next + my_head[r]) : __ldg(next + my_head[r]);
                 const float *rec = shard_record(snap, snap_ld, my_head[r]);
-                float tmp[NW];
-                record_get_uniform<NW, CG ? LD_CG : LD_RO>(rec, tmp);
-                tile_put<NW>(att_s, qa, tmp);
+                if (ASYNC) {
+                    record_copy_async<NW>(att_s + qa * NW, rec);
+                } else {
+                    float tmp[NW];
+                    record_get_uniform<NW, CG ? LD_CG : LD_RO>(rec, tmp);
+                    tile_put<NW>(att_s, qa, tmp);
+                }
                 single_s[qa] = nx < 0;
             }
         }
-        if (lr[r] >= 0 && sev > 0) {
+        if (!ASYNC && lr[r] >= 0 && sev > 0) {
             const int ql = atomicAdd(&ql_len, 1);
             queue_l[ql] = (uint16_t)v;
             if (prefetch && ql < QCAP) {
-                const float *rec = shard_record(snap, snap_ld, lr[r]);
                 float tmp[NW];
-                record_get_uniform<NW, CG ? LD_CG : LD_RO>(rec, tmp);
+                record_get_uniform<NW, CG ? LD_CG : LD_RO>(shard_record(snap, snap_ld, lr[r]), tmp);
                 tile_put<NW>(tch_s, ql, tmp);
             }
         }
     }
+    if (ASYNC) async_copy_wait();
     __syncthreads();
     // ---- phase 1: particles hit by attackers (code/soup.py:56-61 seen from the victim)
     for (int q = tid; q < q_len; q += SBS) {
