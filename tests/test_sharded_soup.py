@@ -112,3 +112,26 @@ def test_evolve_together_single_gpu_falls_back(tmp_path):
         s.evolve(3)
     for x, y in zip(a, b):
         assert x.time == y.time == 3 and torch.equal(x.w.view(torch.int32), y.w.view(torch.int32))
+
+
+def test_evolve_together_plain_loop_on_cpu():
+    """soup.evolve_together on soups without a peer-memory exchange (here: unsharded, oracle backend) is the plain
+    loop: same arenas, uids and generation counters as evolving each soup on its own."""
+    import torch
+    from dist_soup_worker import OracleBackend
+    from soup import PopulationSoup, evolve_together
+    kw = dict(attacking_rate=0.3, learn_from_rate=0.2, train=1, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+
+    def make():
+        soups = [PopulationSoup(k, 512, aggregates=4 if k == 1 else 0, seed=9, backend=OracleBackend(), **kw) for k in (0, 1)]
+        for s in soups:
+            s.track_uids = True
+            s.seed_particles()
+        return soups
+    a, b = make(), make()
+    evolve_together(a, 3)
+    for s in b:
+        s.evolve(3)
+    for x, y in zip(a, b):
+        assert x.time == y.time == 3 and x.next_uid == y.next_uid
+        assert torch.equal(x.w.view(torch.int32), y.w.view(torch.int32)) and torch.equal(x.uid, y.uid)
