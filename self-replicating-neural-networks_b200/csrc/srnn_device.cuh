@@ -212,7 +212,8 @@ SRNN_DEV void ww_apply(const float *op, const float *in, float *out, float one) 
 // ~20 of the general division: with y = rn(1/N) and q0 = rn(a*y) (within one ulp of a/N), the remainder
 // r = a - N*q0 is exact in one FMA and rn(q0 + r*y) is the correctly rounded quotient (Markstein).  The operands here
 // are sums of float32 values, far from the double range limits; an infinite sum stays infinite, NaN stays NaN, and
-// the sums are never -0.  Checked against IEEE division for N = 1..64 on 1.3e9 operands (DESIGN.md "Kernels").
+// the sums are never -0.  Checked against IEEE division for N = 1..64 on 1.3e9 operands; tests/test_div_count_cpu.py
+// repeats the check on 1.2e7 with a C restatement (tests/div_count_check.c).
 template <int N>
 SRNN_DEV double div_count(double a) {
     if constexpr ((N & (N - 1)) == 0) {
