@@ -885,8 +885,10 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 // COMPACTED into a queue and handed to the first threads of the CTA, so whole warps skip a phase instead of every
 // warp executing every path for one or two of its lanes.  Results do not depend on who processes a particle.
 #ifndef SRNN_SOUP_MINB
-#define SRNN_SOUP_MINB 6   // x 128 threads x 2 particles = 1536 particles per SM (shared memory allows no more)
-#endif
+#define SRNN_SOUP_MINB 7   // x 128 threads x 2 particles = 1792 particles per SM: WW(2,2) fits 7 CTAs of 31 KB with the
+#endif                     // partner-prefetch areas at TILE/6 records (SRNN_SOUP_QDIV) and 72 registers (16 B of spills).
+                           // Same-box A/B against 6 CTAs with TILE/4: 10 M particles 0.558 -> 0.529 ms (train 0),
+                           // 0.957 -> 0.946 (train 1), 1 M 0.063 -> 0.059 (profiles/r01_soup_async_ab.txt)
 // Each thread OWNS PPT particles of the tile (particle tid + r*SBS) for the uniform work -- staging, pairing draw,
 // training, cull test -- so the per-tile barriers are paid once per 256 particles and the compacted queues fill a
 // whole warp (about 25 events per phase instead of 12).  77 registers, no spills, 6 CTAs = 1536 particles per SM.
@@ -897,12 +899,15 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 #ifndef SRNN_SOUP_PPT
 #define SRNN_SOUP_PPT 2
 #endif
+#ifndef SRNN_SOUP_QDIV
+#define SRNN_SOUP_QDIV 6   // prefetch areas hold TILE/6 = 40 records per phase (mean 24, sd 5); the rest take the slow path
+#endif
 #ifndef SRNN_SOUP_ASYNC
 #define SRNN_SOUP_ASYNC 1   // cp.async staging of the tile and the partner records (0: through registers)
 #endif
 // shared memory of one CTA: tile + two partner-prefetch areas (TILE/4 records each) + queues (static) and the
 // per-thread SGD scratch (dynamic); shapes whose records are too large for 48 KB keep one particle per thread
-__host__ __device__ constexpr int soup_static_smem(int nw, int ppt) { return nw * 4 * SOUP_BS * ppt * 3 / 2 + 10 * SOUP_BS * ppt + 64; }
+__host__ __device__ constexpr int soup_static_smem(int nw, int ppt) { return nw * 4 * SOUP_BS * ppt * 3 / 2 + 10 * SOUP_BS * ppt + 64; }   // upper bound (QDIV >= 4)
 template <class S>
 __host__ __device__ constexpr int soup_ppt() {
     return soup_static_smem(S::NW, SRNN_SOUP_PPT) + (int)sgd_smem_bytes<S>(SOUP_BS) <= 48 * 1024 ? SRNN_SOUP_PPT : 1;
@@ -918,7 +923,7 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
                                                      uint8_t *action, double *loss, uint8_t *dead_out) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int NW = S::NW, PPT = soup_ppt<S>(), TILE = SBS * PPT;
-    constexpr int QCAP = TILE / 4;   // partner records prefetched per phase and tile (mean TILE/10); beyond: slow path
+    constexpr int QCAP = TILE / SRNN_SOUP_QDIV / 4 * 4;   // partner records prefetched per phase and tile (mean TILE/10); beyond: slow path
     __shared__ __align__(16) float tile[TILE * NW];
     __shared__ __align__(16) float att_s[QCAP * NW];   // the first attacker's record of each queued victim
     __shared__ __align__(16) float tch_s[QCAP * NW];   // the teacher's record of each queued learner
