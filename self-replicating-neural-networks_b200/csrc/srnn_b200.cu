@@ -902,6 +902,12 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 #ifndef SRNN_SOUP_QDIV
 #define SRNN_SOUP_QDIV 6   // prefetch areas hold TILE/6 = 40 records per phase (mean 24, sd 5); the rest take the slow path
 #endif
+// Small soups do not fill the SMs, so residency buys nothing and the 72-register cap only costs (100k particles,
+// train 1: 19 vs 20 us per generation): below SOUP_DENSE_MIN particles per launch the kernels are the 6-CTA build
+// (80 registers, prefetch areas TILE/4), from there on the 7-CTA build.
+constexpr int64_t SOUP_DENSE_MIN = 1 << 19;
+constexpr int SOUP_MINB_SMALL = 6;
+__host__ __device__ constexpr int soup_qdiv(int mb) { return mb >= 7 ? SRNN_SOUP_QDIV : 4; }
 #ifndef SRNN_SOUP_ASYNC
 #define SRNN_SOUP_ASYNC 1   // cp.async staging of the tile and the partner records (0: through registers)
 #endif
@@ -915,7 +921,7 @@ __host__ __device__ constexpr int soup_ppt() {
 template <class S>
 __host__ __device__ constexpr int soup_tile() { return SOUP_BS * soup_ppt<S>(); }   // particles per CTA
 
-template <class S, int SBS, bool CG>
+template <class S, int SBS, bool CG, int QDIV = SRNN_SOUP_QDIV>
 __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const ShardTable &snap, const float *own,
                                                      int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld,
                                                      int64_t slot0, int64_t n, const SoupP &p, uint64_t seed, uint64_t gen,
@@ -923,7 +929,7 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
                                                      uint8_t *action, double *loss, uint8_t *dead_out) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int NW = S::NW, PPT = soup_ppt<S>(), TILE = SBS * PPT;
-    constexpr int QCAP = TILE / SRNN_SOUP_QDIV / 4 * 4;   // partner records prefetched per phase and tile (mean TILE/10); beyond: slow path
+    constexpr int QCAP = TILE / QDIV / 4 * 4;   // partner records prefetched per phase and tile (mean TILE/10); beyond: slow path
     __shared__ __align__(16) float tile[TILE * NW];
     __shared__ __align__(16) float att_s[QCAP * NW];   // the first attacker's record of each queued victim
     __shared__ __align__(16) float tch_s[QCAP * NW];   // the teacher's record of each queued learner
@@ -1099,22 +1105,22 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     tile_stage_out<NW, SBS, TILE>(w_out, out_ld, base, n, tile);
 }
 
-template <class S, int SBS>
-__global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_sync_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
+template <class S, int SBS, int MB>
+__global__ void __launch_bounds__(SBS, MB) soup_sync_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
                                                        int64_t n_total, float *__restrict__ w_out, int64_t out_ld,
                                                        int64_t slot0, int64_t n, SoupP p, uint64_t seed, uint64_t gen,
                                                        Limits lim, const int32_t *__restrict__ head,
                                                        const int32_t *__restrict__ next, uint8_t *action,
                                                        double *loss, uint8_t *dead_out) {
-    soup_tile_generation<S, SBS, false>(blockIdx.x, snap, own, snap_ld, n_total, w_out, out_ld, slot0, n, p, seed, gen, lim,
+    soup_tile_generation<S, SBS, false, soup_qdiv(MB)>(blockIdx.x, snap, own, snap_ld, n_total, w_out, out_ld, slot0, n, p, seed, gen, lim,
                                         head, next, action, loss, dead_out);
 }
 
 // Chained variant for srnn_soup_sync_run (unsharded, many generations): ONE launch per generation.  After its tile
 // generation every thread resets its own list head (consumed) and threads next generation's attack into the OTHER
 // pair of list arrays, so the memset and the separate lists kernel of the per-generation path disappear.
-template <class S, int SBS>
-__global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_chain_kernel(const float *__restrict__ src, int64_t ld,
+template <class S, int SBS, int MB>
+__global__ void __launch_bounds__(SBS, MB) soup_chain_kernel(const float *__restrict__ src, int64_t ld,
                                                                         float *__restrict__ dst, int64_t n, SoupP p,
                                                                         uint64_t seed, uint64_t gen, Limits lim,
                                                                         int32_t *head_cur, const int32_t *next_cur,
@@ -1124,7 +1130,7 @@ __global__ void __launch_bounds__(SBS, SRNN_SOUP_MINB) soup_chain_kernel(const f
     tab.base[0] = src;
     tab.len = n;
     tab.n = 1;
-    soup_tile_generation<S, SBS, false>(blockIdx.x, tab, src, ld, n, dst, ld, 0, n, p, seed, gen, lim, head_cur, next_cur,
+    soup_tile_generation<S, SBS, false, soup_qdiv(MB)>(blockIdx.x, tab, src, ld, n, dst, ld, 0, n, p, seed, gen, lim, head_cur, next_cur,
                                         action, nullptr, dead_out);
 #pragma unroll
     for (int r = 0; r < soup_ppt<S>(); ++r) {
@@ -1813,8 +1819,13 @@ static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, con
     if (snap_ld < S::NW || out_ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s"); \
     constexpr int SBS = SOUP_BS;                                                                             \
     const size_t sm = sgd_smem_bytes<S>(SBS);                                                                \
-    soup_sync_kernel<S, SBS><<<(unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>()), SBS, sm, (cudaStream_t)stream>>>( \
-        tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead);
+    const unsigned grid = (unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>());                             \
+    if (n >= SOUP_DENSE_MIN)                                                                                 \
+        soup_sync_kernel<S, SBS, SRNN_SOUP_MINB><<<grid, SBS, sm, (cudaStream_t)stream>>>(                   \
+            tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead); \
+    else                                                                                                     \
+        soup_sync_kernel<S, SBS, SOUP_MINB_SMALL><<<grid, SBS, sm, (cudaStream_t)stream>>>(                  \
+            tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead);
     SRNN_DISPATCH(d)
 #undef BODY
     return check_launch("srnn_soup_sync");
@@ -1967,8 +1978,13 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
 #define BODY(S)                                                                                              \
     if (ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");                \
     constexpr int SBS = SOUP_BS;                                                                             \
-    soup_chain_kernel<S, SBS><<<(unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>()), SBS, sgd_smem_bytes<S>(SBS), st>>>( \
-        src, ld, dst, n, q, seed, gen, lim, hc, nc, hn, nn, last ? action : nullptr, last ? dead : nullptr, last ? 0 : 1);
+    const unsigned grid = (unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>());                             \
+    if (n >= SOUP_DENSE_MIN)                                                                                 \
+        soup_chain_kernel<S, SBS, SRNN_SOUP_MINB><<<grid, SBS, sgd_smem_bytes<S>(SBS), st>>>(                \
+            src, ld, dst, n, q, seed, gen, lim, hc, nc, hn, nn, last ? action : nullptr, last ? dead : nullptr, last ? 0 : 1); \
+    else                                                                                                     \
+        soup_chain_kernel<S, SBS, SOUP_MINB_SMALL><<<grid, SBS, sgd_smem_bytes<S>(SBS), st>>>(               \
+            src, ld, dst, n, q, seed, gen, lim, hc, nc, hn, nn, last ? action : nullptr, last ? dead : nullptr, last ? 0 : 1);
             SRNN_DISPATCH(d)
 #undef BODY
         }
