@@ -44,6 +44,10 @@ BYTES_PER_NET = 112.0           # 56 B read + 56 B write per resident episode
 # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel at 2^24 nets
 # (profiles/r01_k1_self_apply_fixed_packed_ncu_summary.csv): 940.3 MB + 880.5 MB per launch
 NCU_TRAFFIC_BYTES_PER_NET = (940.291584e6 + 880.501760e6) / (1 << 24)
+# the same for the 10 M-particle soup generation kernel (profiles/r01_soup_sync_10m_ncu.txt)
+SOUP_10M_NCU_TRAFFIC = 1.559e9
+SOUP_10M_NCU_SOURCE = ("ncu dram bytes of one launch at 10 M particles (1.01 GB read + 0.55 GB write), "
+                       "profiles/r01_soup_sync_10m_ncu.txt")
 METRIC = "net self-applications/sec"
 UNIT = "self-applications/s"
 
@@ -149,34 +153,60 @@ def cpu_port_rate(n_nets, seconds):
         done, int(np.log2(n_nets)), N_STEPS)
 
 
+def headline_config(n):
+    """The workload both arms are timed on (identical dict in the B200 line and the --impl reference line)."""
+    return {"workload": "ww22_self_application", "nets_per_gpu": n, "self_applications_per_net": N_STEPS,
+            "net": "WeightwiseNeuralNetwork(width=2, depth=2)", "init": "glorot_uniform",
+            "l2": "inputs larger than L2 (0.94 GB arena per step, fresh arena each step)",
+            "parallelism": "population sharded by net index, no data-path collective"}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_reference(args, rank):
+    """The reference arm: the path's CPU implementation on every host core of the box.  The reference's own Keras /
+    TensorFlow-1.x code cannot be installed (no oracle/_ref), so this is the oracle's SIMD + OpenMP port of
+    WeightwiseNeuralNetwork.apply_to_weights (same pinned arithmetic).  One step = the FULL 2^24-net arena x 100
+    self-applications, exactly the B200 arm's step.  Under torchrun only rank 0 works -- with all cores: the
+    launcher's OMP_NUM_THREADS=1 is overridden."""
     if rank != 0:
         return
-    n = 1 << 20
     import oracle
+    cores = host_cores()
+    oracle.set_threads(cores)
+    n = args.nets
     rng = np.random.default_rng(0)
     lim = np.array([1.0] * 8 + [np.sqrt(1.5)] * 4 + [np.sqrt(2.0)] * 2)
-    w0 = (rng.uniform(-1, 1, (n, 14)) * lim).astype(np.float32)
-    for _ in range(args.warmup):
-        oracle.ww22_self_apply_fast(w0.copy(), N_STEPS)
-    bufs = [w0.copy() for _ in range(args.steps)]
-    t0 = time.perf_counter()
-    for b in bufs:
-        oracle.ww22_self_apply_fast(b, N_STEPS)
-    dt = time.perf_counter() - t0
-    val = n * N_STEPS * args.steps / dt
-    cores = oracle.num_threads()
-    sample = "per step 2^20 of the 2^24 nets x %d self-applications" % N_STEPS
+    w0 = np.empty((n, 14), np.float32)
+    for lo in range(0, n, 1 << 20):
+        hi = min(n, lo + (1 << 20))
+        w0[lo:hi] = (rng.uniform(-1, 1, (hi - lo, 14)) * lim).astype(np.float32)
+    w = np.empty_like(w0)
+    times = []
+    for s in range(args.warmup + args.steps):
+        np.copyto(w, w0)                       # fresh inputs every step, outside the timed region
+        t0 = time.perf_counter()
+        oracle.ww22_self_apply_fast(w, N_STEPS)
+        dt = time.perf_counter() - t0
+        if s >= args.warmup:
+            times.append(dt)
+    total = float(np.sum(times))
+    val = n * N_STEPS * args.steps / total
+    sample = "every step = all 2^%d nets x %d self-applications (nothing sampled down)" % (int(np.log2(n)), N_STEPS)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "ww22_self_application", "nets_per_gpu": N_NETS, "self_applications_per_net": N_STEPS,
-                   "net": "WeightwiseNeuralNetwork(width=2, depth=2)", "l2": "inputs larger than L2"},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": headline_config(n),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "reference Keras/TensorFlow-1.x path unavailable on this box; timed the oracle port "
-                "(same arithmetic, SIMD + OpenMP over nets)"}), flush=True)
+        "note": "reference Keras/TensorFlow-1.x path unavailable on this box; timed the oracle port (same arithmetic, "
+                "AVX-512/AVX2 clones + OpenMP over nets) on all host cores; at N > 1 the value is still ONE host's "
+                "CPU rate -- it does not grow with the number of GPUs"}), flush=True)
 
 
 def _timed(torch, fn, reps=1):
@@ -190,9 +220,18 @@ def _timed(torch, fn, reps=1):
     return e0.elapsed_time(e1) * 1e-3 / reps
 
 
-def secondary_legs(eng, torch, dist, rank, world, dev):
-    """The other half of BASELINE.json's metric (soup generations/s) and the self-training config, device-timed.
-    Reported as extra keys of the JSON line; the headline `value` stays net self-applications/s."""
+def _hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def secondary_legs(eng, torch, dist, rank, world, dev, probe):
+    """The other half of BASELINE.json's metric (soup generations/s) and configs 2-5, device-timed, max over ranks.
+    Reported as extra keys of the JSON line; the headline `value` stays net self-applications/s.
+    Every N: self-training (config 2, weak-scaled), the mixed 10 M soup (config 4), the KFV sweep (config 5, weak-scaled).
+    N = 1 only: the 100k soups of config 3 (a one-GPU config), size sweep, early-stop variant, the class-API facade."""
     from soup import PopulationSoup, evolve_together
     out = {}
 
@@ -202,144 +241,201 @@ def secondary_legs(eng, torch, dist, rank, world, dev):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item()
 
-    if world == 1:
-        # configs[2]: soup of 100k WW, attack 0.1 + self-train 1 epoch, respawn of divergent / zero nets, 1000 generations
-        kw = dict(attacking_rate=0.1, learn_from_rate=-1, train=1, remove_divergent=True, remove_zero=True, epsilon=1e-4)
-        s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, **kw).seed_particles()
-        s.evolve(50)
-        dt = _timed(torch, lambda: s.evolve(1000))
-        out["soup"] = {"metric": "soup generations/sec", "value": 1000 / dt, "unit": "generations/s",
-                       "config": dict(workload="soup_100k_ww", particles=100_000, generations=1000, mode="snapshot-synchronous", **kw),
-                       "particle_generations_per_s": 100_000 * 1000 / dt, "classes_after": s.count()}
-        # the same soup with the reference's exact sequential semantics (dependency-levelled wavefront, bit-identical
-        # to Soup.evolve's particle-by-particle sweep)
-        s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, order="exact", **kw).seed_particles()
-        s.evolve(10)
-        dt = _timed(torch, lambda: s.evolve(200))
-        out["soup_exact_order"] = {"metric": "soup generations/sec", "value": 200 / dt, "unit": "generations/s",
-                                   "config": dict(workload="soup_100k_ww_exact_order", particles=100_000, generations=200,
-                                                  mode="exact sequential order (wavefront)", **kw),
-                                   "rounds_last_generation": s.rounds, "classes_after": s.count()}
-        # same soup at 10M particles, train=0 (configs[3]'s per-GPU regime): one HBM pass per generation
-        kw0 = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, remove_divergent=True, remove_zero=True, epsilon=1e-4)
-        s = PopulationSoup(eng.KIND_WW, 10_000_000, seed=4, **kw0).seed_particles()
-        s.evolve(4)
-        dt = _timed(torch, lambda: s.evolve(20))
-        hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        try:
-            hbm_peak, peak_src = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json"
-        except Exception:
-            pass
-        ach = 10_000_000 * 130.0 * 20 / dt / 1e9
-        out["soup_10m"] = {"metric": "soup generations/sec", "value": 20 / dt, "unit": "generations/s",
-                           "config": dict(workload="soup_10m_ww_train0", particles=10_000_000, generations=20, **kw0),
-                           "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                        "traffic": 1.559e9, "peak_source": peak_src, "kernel": "soup_sync_kernel<WW(2,2)>",
-                                        "algorithmic_bytes": "130 B per particle-generation (112 B own record in/out + 0.2 x 56 B "
-                                                             "partner records + list heads)",
-                                        "traffic_source": "ncu dram bytes of one launch at 10 M particles (1.01 GB read + 0.55 GB write), profiles/r01_soup_sync_10m_ncu.txt"}}
-        del s
-        # configs[2] variant of soup_trajectorys.py:22-24: 30 self-train epochs per particle and generation
-        kw30 = dict(attacking_rate=0.1, learn_from_rate=-1, train=30, remove_divergent=True, remove_zero=True, epsilon=1e-4)
-        s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, **kw30).seed_particles()
-        s.evolve(5)
-        dt = _timed(torch, lambda: s.evolve(100))
-        out["soup_train30"] = {"metric": "soup generations/sec", "value": 100 / dt, "unit": "generations/s",
-                               "config": dict(workload="soup_100k_ww_train30", particles=100_000, generations=100, **kw30),
-                               "self_train_epochs_per_s": 100_000 * 30 * 100 / dt, "classes_after": s.count()}
-        del s
-        # configs[0/1] side figures: the size sweep 2^20 .. 2^27 nets (fresh glorot nets, 100 unconditional steps) and the
-        # early-stop variant (run_net's stop rule, experiment.py:70-77: stop at divergence or fixpoint), which executes
-        # fewer applications per net; both device-timed, one launch each
-        dww = eng.make_desc(eng.KIND_WW, 2, 2)
-        sweep = {}
-        for lg in range(20, 28):
-            pop = eng.Population(dww, 1 << lg).init(seed=lg)
-            if lg == 20:
-                pop.self_apply(N_STEPS)
-                pop.init(seed=lg)
-            sweep["2^%d" % lg] = (1 << lg) * N_STEPS / _timed(torch, lambda: pop.self_apply(N_STEPS))
-            del pop
-        out["size_sweep"] = {"metric": METRIC, "unit": UNIT, "values": sweep}
-        es = {}
-        for eps in (1e-14, 1e-4):
-            pop = eng.Population(dww, N_NETS).init(seed=0)
-            res = {}
-            dt = _timed(torch, lambda: res.update(pop.self_apply(N_STEPS, mode=eng.RUN_UNTIL, eps=eps, want_steps=True,
-                                                                 want_counters=True)))
-            executed = int(res["steps"].sum(dtype=torch.int64).item())
-            es["eps=%g" % eps] = {"nets_per_s": N_NETS / dt, "executed_self_applications_per_s": executed / dt,
-                                  "mean_steps": executed / N_NETS,
-                                  "classes": dict(zip(eng.CLS_NAMES, res["counters"].cpu().tolist()))}
-            del pop
-        out["early_stop"] = {"workload": "ww22_run_net_until_vergence", "nets": N_NETS, "step_limit": N_STEPS, "by_epsilon": es}
-        # configs[4]: known-fixpoint variation sweep, 100 M perturbed identity fixpoints per noise level 1e0 .. 1e-9,
-        # <= 100 self-applications each; means next to the reference's logged values (100 trials per level)
-        dwk = eng.make_desc(eng.KIND_WW, 2, 2)
-        basefix = np.zeros(14, np.float32)
-        basefix[[0, 8, 12]] = 1.0
-        ref_y = [3.63, 5.02, 6.46, 8.04, 9.61, 11.23, 12.99, 14.58, 21.95, 26.45]
-        ref_z = [0, 0, 0, 0, 0.04, 1.38, 3.23, 4.84, 11.91, 16.47]
-        nt, scale, ys, zs, steps_total = 100_000_000, 1.0, [], [], 0.0
-        eng.kfv(dwk, basefix, nt, 1.0, 0, 100, 1e-4, seed=11, want_times=False)
-        t_kfv = 0.0
-        for level in range(10):
-            res = {}
-            t_kfv += _timed(torch, lambda: res.update(eng.kfv(dwk, basefix, nt, scale, level, 100, 1e-4, seed=11, want_times=False)))
-            h = res["hist"].cpu().numpy().astype(np.float64)
-            ys.append(float((h[0] * np.arange(101)).sum() / nt))
-            zs.append(float((h[1] * np.arange(101)).sum() / nt))
-            steps_total += float((h[0] * np.arange(101)).sum()) + nt
-            scale /= 10.0
-        out["kfv_sweep"] = {"metric": "known-fixpoint variation trials/sec", "value": 10 * nt / t_kfv, "unit": "trials/s",
-                            "config": {"workload": "kfv_sweep", "trials_per_level": nt, "levels": "1e0..1e-9", "max_steps": 100,
-                                       "epsilon": 1e-4},
-                            "self_applications_per_s": steps_total / t_kfv,
-                            "mean_steps_to_vergence": ys, "reference_log_steps_to_vergence": ref_y,
-                            "mean_steps_as_fixpoint": zs, "reference_log_steps_as_fixpoint": ref_z}
-        # configs[1]: self-training, 10k WW + 10k AGG(4) x 1000 epochs; and a 2^20-net WW run for throughput
-        dw, da = eng.make_desc(eng.KIND_WW, 2, 2), eng.make_desc(eng.KIND_AGG, 2, 2, 4)
-        pw, pa = eng.Population(dw, 10_000).init(seed=1), eng.Population(da, 10_000).init(seed=1)
-        pw.train(10, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False)
-        dt = _timed(torch, lambda: (pw.train(1000, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False),
-                                    pa.train(1000, want_loss=False)))
-        big = eng.Population(dw, 1 << 20).init(seed=5)
-        big.train(2, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False)
-        dtb = _timed(torch, lambda: big.train(100, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False))
-        out["self_train"] = {"metric": "net self-train epochs/sec", "config_10k_ww_10k_agg_1000_epochs_s": dt,
-                             "value": (1 << 20) * 100 / dtb, "unit": "epochs/s",
-                             "config": {"workload": "ww22_self_train", "nets": 1 << 20, "epochs": 100, "perm": "philox"},
-                             "tflops_algorithmic": (1 << 20) * 100 * 1148.0 / dtb / 1e12,
-                             "classes_10k_ww": dict(zip(eng.CLS_NAMES, pw.classify(1e-4)[1].cpu().tolist()))}
-    else:
-        # configs[3]: mixed soup of 10M nets (one third each WW / AGG / RNN, partners within kind), learn_from + attack,
-        # sharded by particle index over the ranks with one all-gather of the record arena per generation
-        third = (10_000_000 // 3) // world * world
-        kw = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, epsilon=1e-4)
-        gens, res, host = 20, {}, {}
-        for exchange in ("allgather", "auto"):
-            soups = [PopulationSoup(k, third, aggregates=a, seed=5 + k, exchange=exchange, **kw).seed_particles()
-                     for k, a in ((eng.KIND_WW, 0), (eng.KIND_AGG, 4), (eng.KIND_RNN, 0))]
-            for s in soups:
-                s.evolve(2)
+    def barrier():
+        if world > 1:
             dist.barrier()
-            res[soups[0].exchange] = sync_max(_timed(torch, lambda: evolve_together(soups, gens)) / gens)
-            # host time to ENQUEUE a generation (no device sync): shows whether the loop is launch-bound at this N
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            evolve_together(soups, gens)
-            host[soups[0].exchange] = sync_max((time.perf_counter() - t0) / gens)
-            torch.cuda.synchronize()
-            gathered = sum(s.size * s.desc.n_weights * 4 for s in soups)
-            del soups
-            torch.cuda.empty_cache()
-        best = min(res, key=res.get)
-        out["soup"] = {"metric": "soup generations/sec", "value": 1.0 / res[best], "unit": "generations/s",
-                       "config": dict(workload="mixed_soup_10m_sharded", particles=3 * third, kinds="WW/AGG/RNN thirds",
-                                      ranks=world, generations=gens, exchange=best, **kw),
-                       "generations_per_s_by_exchange": {k: 1.0 / v for k, v in res.items()},
-                       "host_enqueue_ms_per_generation": {k: v * 1e3 for k, v in host.items()},
-                       "allgather_bytes_per_generation_per_gpu": gathered}
+        torch.cuda.synchronize()
+
+    def timed(fn):
+        barrier()
+        return sync_max(_timed(torch, fn))
+
+    # ---- configs[1]: self-training.  Per GPU 2^20 WW(2,2) nets x 100 epochs (Philox sample orders), weak-scaled;
+    #      plus the config as written (10k WW + 10k AGG(4) x 1000 epochs) on rank 0's GPU
+    dw, da = eng.make_desc(eng.KIND_WW, 2, 2), eng.make_desc(eng.KIND_AGG, 2, 2, 4)
+    big = eng.Population(dw, 1 << 20).init(seed=5, slot0=rank << 20)
+    big.train(2, perm_mode=eng.PERM_PHILOX, seed=2, slot0=rank << 20, want_loss=False)
+    dtb = timed(lambda: big.train(100, perm_mode=eng.PERM_PHILOX, seed=2, slot0=rank << 20, want_loss=False))
+    pw, pa = eng.Population(dw, 10_000).init(seed=1), eng.Population(da, 10_000).init(seed=1)
+    pw.train(10, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False)
+    dt = _timed(torch, lambda: (pw.train(1000, perm_mode=eng.PERM_PHILOX, seed=2, want_loss=False),
+                                pa.train(1000, want_loss=False)))
+    tf = (1 << 20) * 100 * 1148.0 / dtb / 1e12           # per GPU
+    out["self_train"] = {"metric": "net self-train epochs/sec", "value": world * (1 << 20) * 100 / dtb, "unit": "epochs/s",
+                         "config": {"workload": "ww22_self_train", "nets_per_gpu": 1 << 20, "epochs": 100, "perm": "philox",
+                                    "scaling": "weak"},
+                         "config_10k_ww_10k_agg_1000_epochs_s": dt,
+                         "roofline": {"bound": "fp32", "achieved": tf, "peak": probe * 2 / 1e12, "unit": "TFLOP/s",
+                                      "frac": tf / (probe * 2 / 1e12), "kernel": "train_kernel<WW(2,2)>",
+                                      "algorithmic_flop": "1148 per epoch (14 samples x 82)",
+                                      "fma_pipe_lane_ops": "924 per epoch in the pinned order (update = 3 roundings per weight)",
+                                      "fma_pipe_frac": (1 << 20) * 100 * 924.0 / dtb / probe},
+                         "classes_10k_ww": dict(zip(eng.CLS_NAMES, pw.classify(1e-4)[1].cpu().tolist())),
+                         "classes_10k_agg": dict(zip(eng.CLS_NAMES, pa.classify(1e-4)[1].cpu().tolist()))}
+    del big, pw, pa
+
+    # ---- configs[4]: known-fixpoint variation sweep, per GPU 100 M perturbed identity fixpoints per noise level
+    #      1e0 .. 1e-9, <= 100 self-applications each, weak-scaled (one histogram all-reduce at the end)
+    basefix = np.zeros(14, np.float32)
+    basefix[[0, 8, 12]] = 1.0
+    ref_y = [3.63, 5.02, 6.46, 8.04, 9.61, 11.23, 12.99, 14.58, 21.95, 26.45]
+    ref_z = [0, 0, 0, 0, 0.04, 1.38, 3.23, 4.84, 11.91, 16.47]
+    nt, scale, t_kfv = 100_000_000, 1.0, 0.0
+    eng.kfv(dw, basefix, nt, 1.0, 0, 100, 1e-4, seed=11, slot0=rank * nt, want_times=False)
+    hists = []
+    for level in range(10):
+        res = {}
+        t_kfv += timed(lambda: res.update(eng.kfv(dw, basefix, nt, scale, level, 100, 1e-4, seed=11, slot0=rank * nt,
+                                                  want_times=False)))
+        hists.append(res["hist"])
+        scale /= 10.0
+    h = torch.stack(hists).to(torch.float64)
+    if world > 1:
+        dist.all_reduce(h)
+    h = h.cpu().numpy()
+    steps = np.arange(101)
+    ys = [float((h[l, 0] * steps).sum() / (world * nt)) for l in range(10)]
+    zs = [float((h[l, 1] * steps).sum() / (world * nt)) for l in range(10)]
+    steps_total = float(sum((h[l, 0] * steps).sum() for l in range(10))) + 10.0 * world * nt
+    out["kfv_sweep"] = {"metric": "known-fixpoint variation trials/sec", "value": 10 * world * nt / t_kfv, "unit": "trials/s",
+                        "config": {"workload": "kfv_sweep", "trials_per_level_per_gpu": nt, "levels": "1e0..1e-9",
+                                   "max_steps": 100, "epsilon": 1e-4, "scaling": "weak"},
+                        "self_applications_per_s": steps_total / t_kfv,
+                        "mean_steps_to_vergence": ys, "reference_log_steps_to_vergence": ref_y,
+                        "mean_steps_as_fixpoint": zs, "reference_log_steps_as_fixpoint": ref_z}
+
+    # ---- configs[3]: mixed soup of 10 M nets (one third each WW / AGG / RNN, partners within kind), learn_from + attack.
+    #      N = 1: one owner.  N > 1: sharded by particle index; partner records read from the owning GPU inside the
+    #      generation kernel ("peer") and, for comparison, the per-generation NCCL all-gather the north_star names.
+    third = (10_000_000 // 3) // 8 * 8 // world * world
+    kw = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, epsilon=1e-4)
+    kinds = ((eng.KIND_WW, 0), (eng.KIND_AGG, 4), (eng.KIND_RNN, 0))
+    gens, res, host = 20, {}, {}
+    for exchange in (("allgather", "auto") if world > 1 else ("auto",)):
+        soups = [PopulationSoup(k, third, aggregates=a, seed=5 + k, exchange=exchange, **kw).seed_particles()
+                 for k, a in kinds]
+        evolve_together(soups, 2)
+        res[soups[0].exchange] = timed(lambda: evolve_together(soups, gens)) / gens
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        evolve_together(soups, gens)                 # host time to ENQUEUE a generation (no device sync)
+        host[soups[0].exchange] = sync_max((time.perf_counter() - t0) / gens)
+        torch.cuda.synchronize()
+        del soups
+        torch.cuda.empty_cache()
+    best = min(res, key=res.get)
+    soup = {"metric": "soup generations/sec", "value": 1.0 / res[best], "unit": "generations/s",
+            "config": dict(workload="mixed_soup_10m", particles=3 * third, kinds="WW/AGG/RNN thirds", ranks=world,
+                           generations=gens, exchange=best, scaling="strong", mode="snapshot-synchronous", **kw),
+            "generations_per_s_by_exchange": {k: 1.0 / v for k, v in res.items()},
+            "host_enqueue_ms_per_generation": {k: v * 1e3 for k, v in host.items()},
+            "allgather_bytes_per_generation_per_gpu": sum(third * nw * 4 for nw in (14, 20, 17)) if world > 1 else 0}
+    if world > 1:
+        # parity inside the bench: a sharded soup must equal the same soup owned by ONE process, bit for bit
+        small = 3 * 4096 * world
+        same = True
+        for k, a in kinds:
+            sh = PopulationSoup(k, small, aggregates=a, seed=77, exchange="auto", **kw).seed_particles().evolve(3)
+            one = PopulationSoup(k, small, aggregates=a, seed=77, sharded=False, **kw).seed_particles().evolve(3)
+            mine = one.w[sh.slot0:sh.slot0 + sh.n_local].contiguous().view(torch.int32)
+            same = same and bool(torch.equal(sh.w.contiguous().view(torch.int32), mine))
+            del sh, one
+        flag = torch.tensor([1 if same else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        soup["sharded_equals_single_owner_bitwise"] = bool(flag.item())
+        assert flag.item() == 1, "sharded soup differs from the single-owner soup"
+    out["soup_mixed_10m"] = soup
+    if world > 1:
+        out["soup"] = soup              # key the round-1 driver records read
+        return out
+
+    # ---- N = 1 only below
+    # configs[2]: soup of 100k WW, attack 0.1 + self-train 1 epoch, respawn of divergent / zero nets, 1000 generations
+    kw = dict(attacking_rate=0.1, learn_from_rate=-1, train=1, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+    s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, **kw).seed_particles()
+    s.evolve(50)
+    dt = _timed(torch, lambda: s.evolve(1000))
+    out["soup"] = {"metric": "soup generations/sec", "value": 1000 / dt, "unit": "generations/s",
+                   "config": dict(workload="soup_100k_ww", particles=100_000, generations=1000, mode="snapshot-synchronous", **kw),
+                   "particle_generations_per_s": 100_000 * 1000 / dt, "classes_after": s.count()}
+    # the same soup with the reference's exact sequential semantics (dependency-levelled wavefront, bit-identical
+    # to Soup.evolve's particle-by-particle sweep)
+    s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, order="exact", **kw).seed_particles()
+    s.evolve(10)
+    dt = _timed(torch, lambda: s.evolve(200))
+    out["soup_exact_order"] = {"metric": "soup generations/sec", "value": 200 / dt, "unit": "generations/s",
+                               "config": dict(workload="soup_100k_ww_exact_order", particles=100_000, generations=200,
+                                              mode="exact sequential order (wavefront)", **kw),
+                               "rounds_last_generation": s.rounds, "classes_after": s.count()}
+    # 10 M particles, train=0 (configs[3]'s per-GPU regime): one HBM pass per generation, both orders
+    kw0 = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+    hbm_peak, peak_src = _hbm_peak()
+    s = PopulationSoup(eng.KIND_WW, 10_000_000, seed=4, **kw0).seed_particles()
+    s.evolve(4)
+    dt = _timed(torch, lambda: s.evolve(20))
+    ach = 10_000_000 * 130.0 * 20 / dt / 1e9
+    out["soup_10m"] = {"metric": "soup generations/sec", "value": 20 / dt, "unit": "generations/s",
+                       "config": dict(workload="soup_10m_ww_train0", particles=10_000_000, generations=20, **kw0),
+                       "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                                    "traffic": SOUP_10M_NCU_TRAFFIC, "peak_source": peak_src, "kernel": "soup_sync_kernel<WW(2,2)>",
+                                    "algorithmic_bytes": "130 B per particle-generation (112 B own record in/out + 0.2 x 56 B "
+                                                         "partner records + list heads)",
+                                    "traffic_source": SOUP_10M_NCU_SOURCE}}
+    del s
+    s = PopulationSoup(eng.KIND_WW, 10_000_000, seed=4, order="exact", **kw0).seed_particles()
+    s.evolve(2)
+    dt = _timed(torch, lambda: s.evolve(10))
+    out["soup_10m_exact_order"] = {"metric": "soup generations/sec", "value": 10 / dt, "unit": "generations/s",
+                                   "config": dict(workload="soup_10m_ww_train0_exact_order", particles=10_000_000,
+                                                  generations=10, mode="exact sequential order (wavefront)", **kw0),
+                                   "rounds_last_generation": s.rounds}
+    del s
+    # configs[2] variant of soup_trajectorys.py:22-24: 30 self-train epochs per particle and generation
+    kw30 = dict(attacking_rate=0.1, learn_from_rate=-1, train=30, remove_divergent=True, remove_zero=True, epsilon=1e-4)
+    s = PopulationSoup(eng.KIND_WW, 100_000, seed=3, **kw30).seed_particles()
+    s.evolve(5)
+    dt = _timed(torch, lambda: s.evolve(100))
+    out["soup_train30"] = {"metric": "soup generations/sec", "value": 100 / dt, "unit": "generations/s",
+                           "config": dict(workload="soup_100k_ww_train30", particles=100_000, generations=100, **kw30),
+                           "self_train_epochs_per_s": 100_000 * 30 * 100 / dt, "classes_after": s.count()}
+    del s
+    # configs[0/1] side figures: the size sweep 2^20 .. 2^27 nets (fresh glorot nets, 100 unconditional steps) and the
+    # early-stop variant (run_net's stop rule, experiment.py:70-77: stop at divergence or fixpoint), which executes
+    # fewer applications per net; both device-timed, one launch each
+    sweep = {}
+    for lg in range(20, 28):
+        pop = eng.Population(dw, 1 << lg).init(seed=lg)
+        if lg == 20:
+            pop.self_apply(N_STEPS)
+            pop.init(seed=lg)
+        sweep["2^%d" % lg] = (1 << lg) * N_STEPS / _timed(torch, lambda: pop.self_apply(N_STEPS))
+        del pop
+    out["size_sweep"] = {"metric": METRIC, "unit": UNIT, "values": sweep}
+    es = {}
+    for eps in (1e-14, 1e-4):
+        pop = eng.Population(dw, N_NETS).init(seed=0)
+        res = {}
+        dt = _timed(torch, lambda: res.update(pop.self_apply(N_STEPS, mode=eng.RUN_UNTIL, eps=eps, want_steps=True,
+                                                             want_counters=True)))
+        executed = int(res["steps"].sum(dtype=torch.int64).item())
+        es["eps=%g" % eps] = {"nets_per_s": N_NETS / dt, "executed_self_applications_per_s": executed / dt,
+                              "mean_steps": executed / N_NETS,
+                              "classes": dict(zip(eng.CLS_NAMES, res["counters"].cpu().tolist()))}
+        del pop
+    out["early_stop"] = {"workload": "ww22_run_net_until_vergence", "nets": N_NETS, "step_limit": N_STEPS, "by_epsilon": es}
+    # configs[0] exactly as the reference writes it: 100 nets x 100 self_attack() + count() through the CLASS API (one
+    # Python object and one tiny launch per call), next to the reference-structured NumPy twin on one host core
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import facade_bench
+        from oracle import numpy_twin
+        fac = facade_bench.run()
+        fac["numpy_twin_1core_self_applications_per_s"] = numpy_twin.self_applications_per_second()
+        fac["note"] = ("per-object path: launch- and host-sync-bound by construction (one kernel + one device read per "
+                       "method call); populations go through Soup / srnn_engine")
+        out["facade"] = fac
+    except Exception as exc:        # the facade leg must never take the headline down
+        out["facade"] = {"error": repr(exc)}
     return out
 
 
@@ -351,6 +447,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nets", type=int, default=N_NETS, help="nets per GPU (default 2^24)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--no-legs", action="store_true", help="headline + e2e only (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -382,7 +479,7 @@ def main():
 
     # fresh arenas, one per step (capped by memory: reuse round-robin beyond the cap)
     free = torch.cuda.mem_get_info()[0]
-    cap = max(2, int(free * 0.6 // (n * 56)))
+    cap = max(3, int(free * 0.6 // (n * 56)))
     R = min(K + W, cap)
     arenas = [eng.Population(desc, n).init(seed=1000 + r, slot0=rank * n) for r in range(R)]
     torch.cuda.synchronize()
@@ -415,33 +512,43 @@ def main():
     total_ms, kern_ms = t.tolist()
     value = world * n * N_STEPS * K / (total_ms * 1e-3)
 
-    # ---- end to end: pinned host records -> device -> kernel + classify -> counters to host, double-buffered
-    del arenas[2:]
+    # ---- end to end through the host API with HOST buffers, every step: pinned host records -> device (H2D stream),
+    #      kernel + fused classification (compute stream), final weights AND class counters -> pinned host (D2H stream);
+    #      three arenas in flight so the two copy directions and the kernel overlap
+    NB = 3
+    del arenas[NB:]
     torch.cuda.empty_cache()
-    host = torch.empty((n, 14), dtype=torch.float32).pin_memory()
+    host_in = torch.empty((n, 14), dtype=torch.float32).pin_memory()
     lim = np.array([1.0] * 8 + [1.5 ** .5] * 4 + [2 ** .5] * 2)
-    host.copy_(torch.from_numpy((np.random.default_rng(rank).uniform(-1, 1, (n, 14)) * lim).astype(np.float32)))
-    cnt_host = torch.zeros((2, 5), dtype=torch.int64).pin_memory()
-    copy_stream, comp_stream = torch.cuda.Stream(), torch.cuda.Stream()
-    copied = [torch.cuda.Event() for _ in range(2)]
-    freed = [torch.cuda.Event() for _ in range(2)]
+    host_in.copy_(torch.from_numpy((np.random.default_rng(rank).uniform(-1, 1, (n, 14)) * lim).astype(np.float32)))
+    host_out = [torch.empty((n, 14), dtype=torch.float32).pin_memory() for _ in range(2)]
+    cnt_host = torch.zeros((NB, 5), dtype=torch.int64).pin_memory()
+    cnt_dev = [None] * NB
+    h2d, comp, d2h = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+    copied = [torch.cuda.Event() for _ in range(NB)]
+    done = [torch.cuda.Event() for _ in range(NB)]
+    freed = [torch.cuda.Event() for _ in range(NB)]
 
     def e2e_steps(count):
         for s in range(count):
-            b = s % 2
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(freed[b])
-                arenas[b].w.copy_(host, non_blocking=True)
-                copied[b].record(copy_stream)
-            with torch.cuda.stream(comp_stream):
-                comp_stream.wait_event(copied[b])
-                out = arenas[b].self_apply(N_STEPS, want_counters=True, eps=1e-4)
-                cnt_host[b].copy_(out["counters"], non_blocking=True)
-                freed[b].record(comp_stream)
-        comp_stream.synchronize()
+            b = s % NB
+            with torch.cuda.stream(h2d):
+                h2d.wait_event(freed[b])
+                arenas[b].w.copy_(host_in, non_blocking=True)
+                copied[b].record(h2d)
+            with torch.cuda.stream(comp):
+                comp.wait_event(copied[b])
+                cnt_dev[b] = arenas[b].self_apply(N_STEPS, want_counters=True, eps=1e-4)["counters"]
+                done[b].record(comp)
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(done[b])
+                host_out[s % 2].copy_(arenas[b].w, non_blocking=True)
+                cnt_host[b].copy_(cnt_dev[b], non_blocking=True)
+                freed[b].record(d2h)
+        d2h.synchronize()
 
-    for b in range(2):
-        freed[b].record(comp_stream)
+    for b in range(NB):
+        freed[b].record(d2h)
     e2e_steps(W)
     barrier()
     t0 = time.perf_counter()
@@ -452,23 +559,27 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * n * N_STEPS * K / t.item()
+    e2e_classes = dict(zip(eng.CLS_NAMES, cnt_host[(K - 1) % NB].tolist()))
+    del host_in, host_out
+    del arenas[:]
+    torch.cuda.empty_cache()
 
-    extra = secondary_legs(eng, torch, dist, rank, world, dev)
+    extra = {} if args.no_legs else secondary_legs(eng, torch, dist, rank, world, dev, probe)
 
     if rank == 0:
         achieved_tf = FLOP_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / 1e12
         peak_tf = probe * 2.0 / 1e12
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        theo_tf = sms * 128 * 2 * (clocks["sm_max_mhz"] or 1965.0) * 1e6 / 1e12
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "ww22_self_application", "nets_per_gpu": n, "self_applications_per_net": N_STEPS,
-                       "net": "WeightwiseNeuralNetwork(width=2, depth=2)", "init": "glorot_uniform (Philox)",
-                       "fresh_arenas": R, "l2": "inputs larger than L2 (0.94 GB arena per step, new arena each step)",
-                       "parallelism": "population sharded by net index, no data-path collective",
-                       "host_affinity": ("GPU-local NUMA node, %d cpus" % len(host_cpus)) if host_cpus else "unbound"},
+            "dtype": "f32", "data": "synthetic", "config": headline_config(n),
+            "run": {"fresh_arenas": R, "init_rng": "Philox4x32-10 glorot-uniform on the device",
+                    "host_affinity": ("GPU-local NUMA node, %d cpus" % len(host_cpus)) if host_cpus else "unbound"},
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": 40},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": n * 56 + 40,
+                    "returns": "final weights of every net + the 5 class counters", "classes_last_step": e2e_classes},
             "gpu_launches": K,
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": NCU_TRAFFIC_BYTES_PER_NET * n,
@@ -476,12 +587,16 @@ def main():
                                            "(algorithmic bytes per launch = 112 B x nets)",
                          "kernel": "self_apply_fixed_kernel<WW(2,2)>", "kernel_ms": kern_ms,
                          "peak_source": "FFMA-only probe kernel measured live (MEASURED_PEAKS.json has no FP32 entry)",
+                         "peak_theoretical": theo_tf, "frac_vs_theoretical": achieved_tf / theo_tf,
+                         "peak_theoretical_source": "SMs x 128 lanes x 2 FLOP x max SM clock",
                          "fma_pipe_frac": FP32_INSTR_PER_SELF_APP * n * N_STEPS / (kern_ms * 1e-3) / probe,
                          "hbm_gbs": BYTES_PER_NET * n / (kern_ms * 1e-3) / 1e9},
         }
         line.update(extra)
         if world == 1:
-            v, cores, sample = cpu_port_rate(1 << 20, args.cpu_seconds)
+            import oracle
+            oracle.set_threads(host_cores())
+            v, cores, sample = cpu_port_rate(1 << 22, args.cpu_seconds)
             from oracle import numpy_twin
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                                     "reference_structured_1core": numpy_twin.self_applications_per_second(),

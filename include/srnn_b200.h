@@ -177,7 +177,9 @@ int srnn_assign_uids(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *
  * is a fixed array inside the library image: 128 KiB on every GPU that loads libsrnn_b200.so, kept until the
  * process exits.  n may be at most SRNN_UIDS_STATIC_MAX; larger n is refused with SRNN_ERR_LIMIT.  The call
  * makes no allocation of any kind.  The first call on a device looks up the array's device address (a host-side
- * query with that device current); make that first call before starting any stream capture.  All calls share
+ * query with that device current); make that first call before starting any stream capture.  `stream` must belong
+ * to the device that is current at the time of the call -- the scratch address is the current device's -- and a
+ * stream of another device is refused with SRNN_ERR_ARG.  All calls share
  * the one array per GPU: it needs no clearing between calls (every counter is rewritten before it is read),
  * but two calls whose kernels overlap on the same GPU -- different streams or different host threads --
  * race on it, so keep these calls ordered on one stream per device. */

@@ -251,3 +251,8 @@ def ww22_self_apply_fast(w, n_steps, n=None):
 
 def num_threads():
     return int(lib().srnn_oracle_num_threads())
+
+
+def set_threads(n):
+    """OpenMP team size of the oracle (torchrun exports OMP_NUM_THREADS=1; the CPU baseline wants every core)."""
+    lib().srnn_oracle_set_threads(C.c_int(int(n)))

@@ -108,19 +108,14 @@ static inline void dense(const float *x, const float *W, int in, int out, float 
         y[0] = acc;
     }
 }
-/* g_prev[i] = sum_j g[j] * W[i][j]  (TF: matmul(g, W, transpose_b)); same rules keyed on the
- * number of result units `in` (proposed, unpinned -- SURVEY 8c item 7). */
+/* g_prev[i] = sum_j g[j] * W[i][j]  (TF: matmul(g, W, transpose_b)).  Rule R7a, pinned by the recovered Keras sample
+ * orders (tests/golden/ww_sgd_perms.npz): every result element is a DOT PRODUCT -- products rounded one by one and
+ * added in ascending j, no FMA -- whatever the number of units (the forward GEMM rule R2 does NOT apply here). */
 static inline void dense_T(const float *g, const float *W, int in, int out, float *gp) {
-    if (in >= 2) {
-        for (int i = 0; i < in; ++i) {
-            float acc = g[0] * W[i * out];
-            for (int j = 1; j < out; ++j) acc = fmaf(g[j], W[i * out + j], acc);
-            gp[i] = acc;
-        }
-    } else {
-        float acc = 0.0f;
-        for (int j = 0; j < out; ++j) { float p = g[j] * W[j]; acc = acc + p; }
-        gp[0] = acc;
+    for (int i = 0; i < in; ++i) {
+        float acc = g[0] * W[i * out];
+        for (int j = 1; j < out; ++j) { float p = g[j] * W[i * out + j]; acc = acc + p; }
+        gp[i] = acc;
     }
 }
 
@@ -410,6 +405,7 @@ static inline float u01f(uint32_t x) { return (float)(x >> 8) * 5.96046447753906
 static void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, int n, float *U) {
     uint32_t blk = 0;
     for (int r = 0; r < n; ++r) {
+        int placed = 0;
         for (int attempt = 0; attempt < 64; ++attempt) {
             float v[MAXU];
             float nn = 0.f;
@@ -419,7 +415,7 @@ static void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, in
                 for (int q = 0; q < 4 && c + q < n; ++q) v[c + q] = 2.0f * u01f(x[q]) - 1.0f;
             }
             for (int c = 0; c < n; ++c) nn = nn + v[c] * v[c];
-            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; break; } /* 1x1 orthogonal = +-1 exactly */
+            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; placed = 1; break; } /* 1x1 orthogonal = +-1 exactly */
             if (nn > 1.0f || nn < 1e-4f) continue;           /* outside ball / too short: reject  */
             for (int p = 0; p < r; ++p) {                     /* remove components along earlier rows */
                 float dot = 0.f;
@@ -431,7 +427,13 @@ static void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, in
             if (nn < 1e-2f) continue;
             float inv = 1.0f / sqrtf(nn);
             for (int c = 0; c < n; ++c) U[r * n + c] = v[c] * inv;
+            placed = 1;
             break;
+        }
+        if (!placed) { /* 64 rejections in a row (probability ~ 1e-40): deterministic fallback, the identity matrix */
+            for (int i = 0; i < n; ++i)
+                for (int c = 0; c < n; ++c) U[i * n + c] = i == c ? 1.0f : 0.0f;
+            return;
         }
     }
 }
@@ -538,17 +540,47 @@ static double rnn_sgd_sample(const shape_t *s, float *w, const float *seq, const
     return (double)loss;
 }
 
-/* Fisher-Yates from 16-bit Philox chunks: for i = n-1 .. 1: j = (chunk * (i+1)) >> 16; swap(i, j) */
+/* PERM_PHILOX: the engine's deterministic stand-in for Keras' unseeded per-epoch shuffle (np.random.shuffle inside
+ * model.fit, code/network.py:617).  Fisher-Yates: for i = n-1 .. 1: j = draw(i + 1); swap(perm[i], perm[j]).
+ * Draws come from 32-bit Philox words by exact fixed-point decomposition: j = hi32(r * m), r = lo32(r * m); a word
+ * serves consecutive draws while the product of their ranges stays <= 2^22 (bias <= 2^-10), then the next word is
+ * taken.  An epoch needs W(n) words (2 for n = 14); when W <= 4 one Philox block serves 4 / W consecutive epochs
+ * (block index epoch / EPB, words (epoch % EPB) * W ...), else ceil(W / 4) blocks per epoch. */
+static int perm_words_needed(int n) {
+    int wi = -1;
+    uint32_t prod = 1;
+    for (int i = n - 1; i >= 1; --i) {
+        uint32_t m = (uint32_t)i + 1;
+        if (wi < 0 || (uint64_t)prod * m > (1u << 22)) { ++wi; prod = 1; }
+        prod *= m;
+    }
+    return wi + 1;
+}
 static void philox_perm(uint64_t seed, uint64_t slot, uint64_t epoch, int n, uint8_t *perm) {
     for (int i = 0; i < n; ++i) perm[i] = (uint8_t)i;
-    uint32_t x[4];
-    int have = 0, blk = 0;
+    if (n < 2) return;
+    const int W = perm_words_needed(n);
+    const int EPB = W <= 4 ? 4 / W : 1;
+    const uint64_t E = epoch / (uint64_t)EPB;
+    const int o = (int)(epoch % (uint64_t)EPB) * W;
+    uint32_t x[4], r = 0, prod = 1;
+    int wi = -1, cur_blk = -1;
     for (int i = n - 1; i >= 1; --i) {
-        if ((have & 7) == 0) rng4(seed, ST_PERM, slot, (uint32_t)epoch, ((uint32_t)(epoch >> 32) << 8) | (uint32_t)blk++, x);
-        uint32_t word = x[(have & 7) >> 1];
-        uint32_t chunk = (have & 1) ? (word >> 16) : (word & 0xFFFFu);
-        ++have;
-        int j = (int)((chunk * (uint32_t)(i + 1)) >> 16);
+        uint32_t m = (uint32_t)i + 1;
+        if (wi < 0 || (uint64_t)prod * m > (1u << 22)) {
+            ++wi;
+            prod = 1;
+            int g = o + wi, blk = g >> 2;
+            if (blk != cur_blk) {
+                rng4(seed, ST_PERM, slot, (uint32_t)E, ((uint32_t)(E >> 32) << 8) | (uint32_t)blk, x);
+                cur_blk = blk;
+            }
+            r = x[g & 3];
+        }
+        prod *= m;
+        uint64_t wide = (uint64_t)r * m;
+        int j = (int)(wide >> 32);
+        r = (uint32_t)wide;
         uint8_t tmp = perm[i]; perm[i] = perm[j]; perm[j] = tmp;
     }
 }
@@ -824,12 +856,37 @@ int srnn_oracle_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, con
 /* WW(2,2) self-application, same pinned arithmetic, restructured for the host's SIMD units: blocks of 64
  * records are transposed into planes so the inner loop runs over nets and gcc vectorises the fma chains.  Used as the "strong CPU baseline"
  * of bench.py; checked against srnn_oracle_self_apply in the CPU tests. */
-int srnn_oracle_ww22_self_apply_fast(float *w, int64_t ld, int64_t n, int32_t n_steps) {
+enum { FAST_B = 64 };
+/* n_steps self-applications of a block of 64 nets held as weight planes.  Compiled three times (AVX-512, AVX2+FMA,
+ * baseline) and dispatched on the CPU the code runs on, so the library built in the container uses the widest SIMD
+ * of the GPU box's host without -march=native.  fmaf stays one IEEE fma in every clone (libm call in the baseline). */
+__attribute__((target_clones("arch=x86-64-v4", "arch=x86-64-v3", "default")))
+static void ww22_block_steps(float (*cur)[FAST_B], float (*nxt)[FAST_B], int n_steps) {
     static const float L[14] = {0, 0, 0, 0, 0, 0, 0, 0, .5f, .5f, .5f, .5f, 1, 1};
     const float third = (float)(1.0 / 3.0), two3 = (float)(2.0 / 3.0);
     const float R[14] = {0, 0, third, third, two3, two3, 1, 1, 0, 0, 1, 1, 0, 1};
     static const float C[14] = {0, 1, 0, 1, 0, 1, 0, 1, 0, 1, 0, 1, 0, 0};
-    enum { B = 64 };
+    for (int st = 0; st < n_steps; ++st) {
+        for (int k = 0; k < 14; ++k) {
+            const float l = L[k], r = R[k], c = C[k];
+#pragma omp simd
+            for (int i = 0; i < FAST_B; ++i) {
+                float x = cur[k][i];
+                float h0 = x * cur[0][i], h1 = x * cur[1][i];
+                h0 = fmaf(l, cur[2][i], h0); h1 = fmaf(l, cur[3][i], h1);
+                h0 = fmaf(r, cur[4][i], h0); h1 = fmaf(r, cur[5][i], h1);
+                h0 = fmaf(c, cur[6][i], h0); h1 = fmaf(c, cur[7][i], h1);
+                float g0 = h0 * cur[8][i], g1 = h0 * cur[9][i];
+                g0 = fmaf(h1, cur[10][i], g0); g1 = fmaf(h1, cur[11][i], g1);
+                float p0 = g0 * cur[12][i], p1 = g1 * cur[13][i];
+                nxt[k][i] = (0.0f + p0) + p1;
+            }
+        }
+        memcpy(cur, nxt, sizeof(float) * 14 * FAST_B);
+    }
+}
+int srnn_oracle_ww22_self_apply_fast(float *w, int64_t ld, int64_t n, int32_t n_steps) {
+    enum { B = FAST_B };
 #pragma omp parallel
     {
         unsigned csr = ftz_on();
@@ -841,30 +898,20 @@ int srnn_oracle_ww22_self_apply_fast(float *w, int64_t ld, int64_t n, int32_t n_
                 for (int i = 0; i < m; ++i) cur[k][i] = w[(i0 + i) * ld + k];
             for (int k = 0; k < 14; ++k)
                 for (int i = m; i < B; ++i) cur[k][i] = 0.f;
-            for (int st = 0; st < n_steps; ++st) {
-                for (int k = 0; k < 14; ++k) {
-                    const float l = L[k], r = R[k], c = C[k];
-#pragma omp simd
-                    for (int i = 0; i < B; ++i) {
-                        float x = cur[k][i];
-                        float h0 = x * cur[0][i], h1 = x * cur[1][i];
-                        h0 = fmaf(l, cur[2][i], h0); h1 = fmaf(l, cur[3][i], h1);
-                        h0 = fmaf(r, cur[4][i], h0); h1 = fmaf(r, cur[5][i], h1);
-                        h0 = fmaf(c, cur[6][i], h0); h1 = fmaf(c, cur[7][i], h1);
-                        float g0 = h0 * cur[8][i], g1 = h0 * cur[9][i];
-                        g0 = fmaf(h1, cur[10][i], g0); g1 = fmaf(h1, cur[11][i], g1);
-                        float p0 = g0 * cur[12][i], p1 = g1 * cur[13][i];
-                        nxt[k][i] = (0.0f + p0) + p1;
-                    }
-                }
-                memcpy(cur, nxt, sizeof cur);
-            }
+            ww22_block_steps(cur, nxt, n_steps);
             for (int k = 0; k < 14; ++k)
                 for (int i = 0; i < m; ++i) w[(i0 + i) * ld + k] = cur[k][i];
         }
         ftz_restore(csr);
     }
     return SRNN_OK;
+}
+
+/* bench.py --impl reference under torchrun: the launcher exports OMP_NUM_THREADS=1, which would time one core */
+void srnn_oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#endif
 }
 
 int srnn_oracle_num_threads(void) {

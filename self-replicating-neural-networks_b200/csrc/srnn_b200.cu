@@ -558,19 +558,44 @@ __global__ void __launch_bounds__(BS) train_kernel(float *__restrict__ w, int64_
         }
         double loss = 0.0;
         const bool ordered = S::NS > 1 && perm_mode != SRNN_PERM_NONE;
-        for (int e = 0; e < n_epochs; ++e) {
-            if (!teacher_w) {  // targets frozen at the start of the epoch, code/network.py:615
+        if constexpr (S::KIND == SRNN_KIND_WW && S::NW <= 16) {
+            // fast path: sample loop unrolled, order in one register, Philox block shared by EPB epochs
+            U4 blk;
+            uint64_t blk_id = ~0ull;
+            for (int e = 0; e < n_epochs; ++e) {
+                if (!teacher_w) {  // targets frozen at the start of the epoch, code/network.py:615
 #pragma unroll
-                for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = cur[k];
-            }
-            if (ordered) {
-                if (perm_mode == SRNN_PERM_EXPLICIT) {
-                    for (int q = 0; q < S::NS; ++q) sc.ord[q * sc.stride] = perm[(int64_t)e * S::NS + q];
-                } else {
-                    philox_perm<S::NS>(seed, slot0 + (uint64_t)i, epoch0 + (uint64_t)e, sc.ord, sc.stride);
+                    for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = cur[k];
                 }
+                uint64_t order = 0;
+                if (perm_mode == SRNN_PERM_EXPLICIT) {
+#pragma unroll
+                    for (int q = 0; q < S::NS; ++q) order |= (uint64_t)(perm[(int64_t)e * S::NS + q] & 15u) << (4 * q);
+                } else if (perm_mode == SRNN_PERM_PHILOX) {
+                    uint32_t r[PermPlan<S::NS>::W];
+                    perm_words<S::NS>(seed, slot0 + (uint64_t)i, epoch0 + (uint64_t)e, r, blk, blk_id);
+                    order = perm_nibbles<S::NS>(r);
+                }
+                const bool last = loss_out != nullptr && e == n_epochs - 1;
+                if (!ordered) loss = ww_epoch_unrolled<S, false, true>(cur, sc.tgt, sc.stride, sc.codes, 0, lr, sc.one);
+                else if (last) loss = ww_epoch_unrolled<S, true, true>(cur, sc.tgt, sc.stride, sc.codes, order, lr, sc.one);
+                else ww_epoch_unrolled<S, true, false>(cur, sc.tgt, sc.stride, sc.codes, order, lr, sc.one);
             }
-            loss = train_epoch<S>(cur, sc, ordered, lr, loss_out != nullptr && e == n_epochs - 1);
+        } else {
+            for (int e = 0; e < n_epochs; ++e) {
+                if (!teacher_w) {  // targets frozen at the start of the epoch, code/network.py:615
+#pragma unroll
+                    for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+                }
+                if (ordered) {
+                    if (perm_mode == SRNN_PERM_EXPLICIT) {
+                        for (int q = 0; q < S::NS; ++q) sc.ord[q * sc.stride] = perm[(int64_t)e * S::NS + q];
+                    } else {
+                        philox_perm<S::NS>(seed, slot0 + (uint64_t)i, epoch0 + (uint64_t)e, sc.ord, sc.stride);
+                    }
+                }
+                loss = train_epoch<S>(cur, sc, ordered, lr, loss_out != nullptr && e == n_epochs - 1);
+            }
         }
         if (loss_out) loss_out[i] = loss;
     }
@@ -1770,6 +1795,13 @@ int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *
     return check_launch("srnn_soup_ordered");
 }
 
+// [a, a + na*lda) and [b, b + nb*ldb) as address ranges (floats); used to refuse outputs that overlap the snapshot
+static bool ranges_overlap(const float *a, int64_t na, int64_t lda, const float *b, int64_t nb, int64_t ldb) {
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(a), a1 = a0 + sizeof(float) * (size_t)(na * lda);
+    const uintptr_t b0 = reinterpret_cast<uintptr_t>(b), b1 = b0 + sizeof(float) * (size_t)(nb * ldb);
+    return a0 < b1 && b0 < a1;
+}
+
 static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, const ShardTable &tab, const float *own,
                           int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n,
                           uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead,
@@ -1835,7 +1867,8 @@ int srnn_soup_sync(const srnn_net_desc *d, const srnn_soup_params *p, const floa
                    int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n, uint64_t seed, uint64_t gen,
                    int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream) {
     if (!snap || !w_out) return fail(SRNN_ERR_ARG, "arena pointer is NULL%s");
-    if ((const float *)w_out == snap) return fail(SRNN_ERR_ARG, "w_out must not alias snap%s");
+    if (n > 0 && n_total > 0 && ranges_overlap(w_out, n, out_ld, snap, n_total, snap_ld))
+        return fail(SRNN_ERR_ARG, "w_out must not overlap snap (partner records are read while w_out is written)%s");
     ShardTable tab;
     memset(&tab, 0, sizeof tab);
     tab.base[0] = snap;
@@ -1855,7 +1888,8 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
     memset(&tab, 0, sizeof tab);
     for (int r = 0; r < n_shards; ++r) {
         if (!shards[r]) return fail(SRNN_ERR_ARG, "a shard pointer is NULL%s");
-        if (shards[r] == w_out) return fail(SRNN_ERR_ARG, "w_out must not alias a shard%s");
+        if (shard_len > 0 && ranges_overlap(w_out, shard_len, out_ld, shards[r], shard_len, ld))
+            return fail(SRNN_ERR_ARG, "w_out must not overlap a shard%s");
         tab.base[r] = shards[r];
     }
     tab.len = shard_len;
@@ -1870,6 +1904,8 @@ int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w,
     if (!d || !scratch) return fail(SRNN_ERR_ARG, "desc or scratch is NULL%s");
     if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
     if (n >= 0x7fffffffLL) return fail(SRNN_ERR_ARG, "need n < 2^31%s");
+    if ((att == nullptr) != (lrn == nullptr))
+        return fail(SRNN_ERR_ARG, "srnn_soup_exact: pass both att and lrn (explicit pairings) or neither (Philox draws)%s");
     SoupP q;
     int rc = make_soup(p, &q);
     if (rc) return rc;
@@ -2051,6 +2087,16 @@ int srnn_assign_uids_static(const uint8_t *dead, int64_t n, int64_t uid_base, in
     int64_t *scratch = nullptr;
     int rc = uid_scratch_of_current_device(&scratch);   // first call on a device resolves the symbol address
     if (rc) return rc;
+    // The array that was just looked up belongs to the CURRENT device.  A stream created on another GPU would run the
+    // kernels there, against that GPU's inputs but this GPU's scratch address: refuse it instead of corrupting memory.
+    {
+        int cur = -1, sdev = -1;
+        if (cudaGetDevice(&cur) == cudaSuccess && cudaStreamGetDevice((cudaStream_t)stream, &sdev) == cudaSuccess &&
+            sdev != cur)
+            return fail(SRNN_ERR_ARG, "srnn_assign_uids_static: the stream belongs to another device than the current "
+                                      "one; make the stream's device current before the call%s");
+        (void)cudaGetLastError();   // a failed query (very old driver) is not an error of this call
+    }
     // Nothing in the scratch has to start from zero: every counter that is read was written earlier in this
     // same call (counts -> scan -> offsets), so whatever an earlier call left behind is never observed.
     const int64_t nb = (n + SCAN_BS - 1) / SCAN_BS;

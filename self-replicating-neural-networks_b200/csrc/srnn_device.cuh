@@ -148,22 +148,17 @@ SRNN_DEV void dense(const float *x, const float *W, float *y) {
         y[0] = acc;
     }
 }
-// gp[i] = sum_j g[j] * W[i][j]   (backward of Dense; same rules keyed on the IN result units)
+// gp[i] = sum_j g[j] * W[i][j]   (backward of Dense).  Rule R7a, pinned by the Keras sample orders recovered from the
+// reference's self-training trajectories: a dot product per result element -- products rounded one by one and added in
+// ascending j, never fused -- whatever the number of units.
 template <int IN, int OUT>
 SRNN_DEV void dense_T(const float *g, const float *W, float *gp) {
-    if constexpr (IN >= 2) {
 #pragma unroll
-        for (int i = 0; i < IN; ++i) {
-            float acc = __fmul_rn(g[0], W[i * OUT]);
+    for (int i = 0; i < IN; ++i) {
+        float acc = __fmul_rn(g[0], W[i * OUT]);
 #pragma unroll
-            for (int j = 1; j < OUT; ++j) acc = __fmaf_rn(g[j], W[i * OUT + j], acc);
-            gp[i] = acc;
-        }
-    } else {
-        float acc = 0.0f;
-#pragma unroll
-        for (int j = 0; j < OUT; ++j) acc = __fadd_rn(acc, __fmul_rn(g[j], W[j]));
-        gp[0] = acc;
+        for (int j = 1; j < OUT; ++j) acc = __fadd_rn(acc, __fmul_rn(g[j], W[i * OUT + j]));
+        gp[i] = acc;
     }
 }
 
@@ -357,6 +352,7 @@ SRNN_DEV void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, 
     const int n = layer == S::NL - 1 ? S::OUTW : S::WIDTH;
     uint32_t blk = 0;
     for (int r = 0; r < n; ++r) {
+        bool placed = false;
         for (int attempt = 0; attempt < 64; ++attempt) {
             float v[NMAX];
             for (int c = 0; c < n; c += 4) {
@@ -366,7 +362,7 @@ SRNN_DEV void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, 
             }
             float nn = 0.f;
             for (int c = 0; c < n; ++c) nn = __fadd_rn(nn, __fmul_rn(v[c], v[c]));
-            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; break; }  // 1x1 orthogonal = +-1 exactly
+            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; placed = true; break; }  // 1x1 orthogonal = +-1 exactly
             if (nn > 1.0f || nn < 1e-4f) continue;
             for (int p = 0; p < r; ++p) {
                 float dot = 0.f;
@@ -378,7 +374,13 @@ SRNN_DEV void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, 
             if (nn < 1e-2f) continue;
             const float inv = __fdiv_rn(1.0f, __fsqrt_rn(nn));
             for (int c = 0; c < n; ++c) U[r * n + c] = __fmul_rn(v[c], inv);
+            placed = true;
             break;
+        }
+        if (!placed) {   // 64 rejections in a row (probability ~ 1e-40): deterministic fallback, the identity matrix
+            for (int i = 0; i < n; ++i)
+                for (int c = 0; c < n; ++c) U[i * n + c] = i == c ? 1.0f : 0.0f;
+            return;
         }
     }
 }
@@ -424,12 +426,13 @@ SRNN_DEV float mlp_sgd_sample(float *w, const float *x, const float *y, float lr
     for (int j = 0; j < NO; ++j) {
         const float dlt = __fsub_rn(act[S::NL][j], y[j]);
         tot = __fadd_rn(tot, __fmul_rn(dlt, dlt));
-        g[j] = __fmul_rn(inv, __fmul_rn(2.0f, dlt));
+        // one output unit: 1/n_out = 1 and rn(1 * x) = x for the flushed x = rn(2 * dlt), so the multiply is dropped
+        g[j] = NO == 1 ? __fmul_rn(2.0f, dlt) : __fmul_rn(inv, __fmul_rn(2.0f, dlt));
     }
     // tot / n_out: for a power-of-two n_out the multiplication by 1/n_out is the same rounding and avoids the
     // division subroutine in the sample loop
     constexpr bool POW2 = (NO & (NO - 1)) == 0;
-    const float loss = POW2 ? __fmul_rn(tot, 1.0f / (float)NO) : __fdiv_rn(tot, (float)NO);
+    const float loss = NO == 1 ? tot : (POW2 ? __fmul_rn(tot, 1.0f / (float)NO) : __fdiv_rn(tot, (float)NO));
     static_rfor<S::NL>([&](auto LL) {
         constexpr int l = decltype(LL)::value;
         constexpr int IN = S::in(l), OUT = S::out(l);
@@ -549,27 +552,106 @@ struct SgdScratch {
     float one;        // opaque_one(), fetched once per thread
 };
 
-// Fisher-Yates from 16-bit Philox chunks: for i = n-1 .. 1: j = (chunk * (i+1)) >> 16; swap(i, j).  Draw d (0-based)
-// uses half (d & 1) of word (d % 8) / 2 of Philox block d / 8.  Fully unrolled: every index but j is a constant.
+// PERM_PHILOX sample orders: the deterministic stand-in for Keras' unseeded per-epoch shuffle.  Fisher-Yates,
+// for i = NS-1 .. 1: j = draw(i + 1); swap(perm[i], perm[j]).  Draws come from 32-bit Philox words by exact fixed-point
+// decomposition, j = hi32(r * m), r = lo32(r * m); a word serves consecutive draws while the product of their ranges
+// stays <= 2^22, then the next word is taken (oracle: philox_perm in oracle/srnn_oracle.c).  An epoch needs W words
+// (2 for the 14 samples of WW(2,2)); one Philox block serves EPB = 4 / W consecutive epochs.
+template <int NS>
+struct PermPlan {
+    static constexpr int NDRAW = NS > 0 ? NS - 1 : 0;
+    static SRNN_HD int word_of_draw(int d) {   // draw d = 0 .. NDRAW-1 has range m = NS - d
+        int wi = 0;
+        unsigned prod = 1;
+        for (int dd = 0; dd <= d; ++dd) {
+            const unsigned m = (unsigned)(NS - dd);
+            if (dd > 0 && (unsigned long long)prod * m > (1u << 22)) { ++wi; prod = 1; }
+            prod *= m;
+        }
+        return wi;
+    }
+    static constexpr int W = NDRAW > 0 ? word_of_draw(NDRAW - 1) + 1 : 1;
+    static_assert(W <= 4, "fixed shapes need at most one Philox block per epoch");
+    static constexpr int EPB = 4 / W;
+};
+// the epoch's W words; `blk` caches the Philox block across the EPB epochs it serves (blk_id = its index, ~0 = none)
+template <int NS>
+SRNN_DEV void perm_words(uint64_t seed, uint64_t slot, uint64_t epoch, uint32_t *r, U4 &blk, uint64_t &blk_id) {
+    using P = PermPlan<NS>;
+    const uint64_t E = epoch / (uint64_t)P::EPB;
+    if (E != blk_id) {
+        blk = rng4(seed, ST_PERM, slot, (uint32_t)E, (uint32_t)(E >> 32) << 8);
+        blk_id = E;
+    }
+    const int o = (int)(epoch % (uint64_t)P::EPB) * P::W;
+#pragma unroll
+    for (int wi = 0; wi < P::W; ++wi) r[wi] = P::EPB == 1 ? word_of(blk, wi) : word_of(blk, o + wi);
+}
+// orders of up to 16 samples live in ONE 64-bit register, 4 bits per position (sample q runs weight point
+// (p >> 4q) & 15): no shared memory, the 13 swaps are shifts and xors
+template <int NS>
+SRNN_DEV uint64_t perm_nibbles(const uint32_t *r_in) {
+    using P = PermPlan<NS>;
+    static_assert(NS <= 16, "nibble-packed orders hold 16 samples");
+    uint32_t r[P::W];
+#pragma unroll
+    for (int wi = 0; wi < P::W; ++wi) r[wi] = r_in[wi];
+    uint64_t p = 0xFEDCBA9876543210ull;
+    static_for<0, P::NDRAW>([&](auto D) {
+        constexpr int d = decltype(D)::value, i = NS - 1 - d, wi = P::word_of_draw(d);
+        constexpr uint32_t m = (uint32_t)(i + 1);
+        const uint32_t sj = __umulhi(r[wi], m) << 2;
+        r[wi] *= m;
+        const uint32_t x = ((uint32_t)(p >> (4 * i)) ^ (uint32_t)(p >> sj)) & 15u;
+        p ^= ((uint64_t)x << (4 * i)) ^ ((uint64_t)x << sj);
+    });
+    return p;
+}
+// larger sample counts keep the order as bytes in shared memory, one column per thread
 template <int NS>
 SRNN_DEV void philox_perm(uint64_t seed, uint64_t slot, uint64_t epoch, uint8_t *ord, int stride) {
+    using P = PermPlan<NS>;
+    uint32_t r[P::W];
+    U4 blk;
+    uint64_t blk_id = ~0ull;
+    perm_words<NS>(seed, slot, epoch, r, blk, blk_id);
+    if constexpr (NS <= 16) {
+        const uint64_t p = perm_nibbles<NS>(r);
 #pragma unroll
-    for (int i = 0; i < NS; ++i) ord[i * stride] = (uint8_t)i;
-    constexpr int NDRAW = NS - 1, NBLK = (NDRAW + 7) / 8;
-    U4 x[NBLK > 0 ? NBLK : 1];
+        for (int q = 0; q < NS; ++q) ord[q * stride] = (uint8_t)((uint32_t)(p >> (4 * q)) & 15u);
+    } else {
 #pragma unroll
-    for (int b = 0; b < NBLK; ++b)
-        x[b] = rng4(seed, ST_PERM, slot, (uint32_t)epoch, ((uint32_t)(epoch >> 32) << 8) | (uint32_t)b);
-    static_for<0, NDRAW>([&](auto D) {
-        constexpr int d = decltype(D)::value, i = NS - 1 - d;
-        constexpr int blk = d / 8, w = (d % 8) / 2;
-        const uint32_t word = w == 0 ? x[blk].x : (w == 1 ? x[blk].y : (w == 2 ? x[blk].z : x[blk].w));
-        const uint32_t chunk = (d & 1) ? (word >> 16) : (word & 0xFFFFu);
-        const int j = (int)((chunk * (uint32_t)(i + 1)) >> 16);
-        const uint8_t tmp = ord[i * stride];
-        ord[i * stride] = ord[j * stride];
-        ord[j * stride] = tmp;
+        for (int i = 0; i < NS; ++i) ord[i * stride] = (uint8_t)i;
+        static_for<0, P::NDRAW>([&](auto D) {
+            constexpr int d = decltype(D)::value, i = NS - 1 - d, wi = P::word_of_draw(d);
+            constexpr uint32_t m = (uint32_t)(i + 1);
+            const int j = (int)__umulhi(r[wi], m);
+            r[wi] *= m;
+            const uint8_t tmp = ord[i * stride];
+            ord[i * stride] = ord[j * stride];
+            ord[j * stride] = tmp;
+        });
+    }
+}
+
+// One epoch of a weightwise net with the sample loop unrolled: sample q's weight point comes out of the nibble-packed
+// order with one shift (ORDERED) or is q itself; target and position codes are fetched from shared memory by that
+// index.  The f64 loss accumulation only exists in the WANT_LOSS instantiation (the last epoch of a call).
+template <class S, bool ORDERED, bool WANT_LOSS>
+SRNN_DEV double ww_epoch_unrolled(float *w, const float *tgt, int stride, const float *codes, uint64_t order, float lr,
+                                  float one) {
+    static_assert(S::KIND == SRNN_KIND_WW && S::NW <= 16, "unrolled epoch: weightwise nets of up to 16 weights");
+    double acc = 0.0;
+    static_for<0, S::NW>([&](auto Q) {
+        constexpr int q = decltype(Q)::value;
+        const uint32_t k = ORDERED ? ((uint32_t)(order >> (4 * q)) & 15u) : (uint32_t)q;
+        const float v = tgt[k * stride];
+        const float x[4] = {v, codes[k], codes[S::NW + k], codes[2 * S::NW + k]};
+        const float l = mlp_sgd_sample<S>(w, x, &v, lr, one);
+        if constexpr (WANT_LOSS) acc = __dadd_rn(acc, (double)l);
     });
+    if constexpr (WANT_LOSS) return div_count<S::NW>(acc);
+    return 0.0;
 }
 
 // One Keras epoch of the student `w` on the samples frozen in sc.tgt; returns the f64 mean sample loss.

@@ -75,17 +75,11 @@ __device__ inline void dense(const float *x, const float *W, int in, int out, fl
         y[0] = acc;
     }
 }
-__device__ inline void dense_T(const float *g, const float *W, int in, int out, float *gp) {
-    if (in >= 2) {
-        for (int i = 0; i < in; ++i) {
-            float acc = __fmul_rn(g[0], W[i * out]);
-            for (int j = 1; j < out; ++j) acc = __fmaf_rn(g[j], W[i * out + j], acc);
-            gp[i] = acc;
-        }
-    } else {
+__device__ inline void dense_T(const float *g, const float *W, int in, int out, float *gp) {   // rule R7a: dot products
+    for (int i = 0; i < in; ++i) {
         float acc = 0.0f;
-        for (int j = 0; j < out; ++j) acc = __fadd_rn(acc, __fmul_rn(g[j], W[j]));
-        gp[0] = acc;
+        for (int j = 0; j < out; ++j) acc = __fadd_rn(acc, __fmul_rn(g[j], W[i * out + j]));
+        gp[i] = acc;
     }
 }
 __device__ inline void mlp_forward(const DynShape &s, const float *w, const float *x, float *y) {
@@ -179,6 +173,7 @@ __device__ inline int classify_with(const DynShape &s, const float *w, const flo
 __device__ inline void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, int layer, int n, float *U) {
     uint32_t blk = 0;
     for (int r = 0; r < n; ++r) {
+        bool placed = false;
         for (int attempt = 0; attempt < 64; ++attempt) {
             float v[MAXU];
             for (int c = 0; c < n; c += 4) {
@@ -187,7 +182,7 @@ __device__ inline void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, in
             }
             float nn = 0.f;
             for (int c = 0; c < n; ++c) nn = __fadd_rn(nn, __fmul_rn(v[c], v[c]));
-            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; break; }
+            if (n == 1) { U[0] = v[0] < 0.f ? -1.0f : 1.0f; placed = true; break; }
             if (nn > 1.0f || nn < 1e-4f) continue;
             for (int p = 0; p < r; ++p) {
                 float dot = 0.f;
@@ -199,7 +194,13 @@ __device__ inline void ortho_rows(uint64_t seed, uint64_t slot, uint32_t gen, in
             if (nn < 1e-2f) continue;
             const float inv = __fdiv_rn(1.0f, __fsqrt_rn(nn));
             for (int c = 0; c < n; ++c) U[r * n + c] = __fmul_rn(v[c], inv);
+            placed = true;
             break;
+        }
+        if (!placed) {   // 64 rejections in a row (probability ~ 1e-40): deterministic fallback, the identity matrix
+            for (int i = 0; i < n; ++i)
+                for (int c = 0; c < n; ++c) U[i * n + c] = i == c ? 1.0f : 0.0f;
+            return;
         }
     }
 }
@@ -287,17 +288,42 @@ __device__ inline float rnn_sgd_sample(const DynShape &s, float *w, const float 
     for (int k = 0; k < s.n_weights; ++k) w[k] = __fsub_rn(w[k], __fmul_rn(lr, dW[k]));
     return loss;
 }
+// same definition as PermPlan / philox_perm of srnn_device.cuh and the oracle, with the word schedule found at run time
 __device__ inline void philox_perm(uint64_t seed, uint64_t slot, uint64_t epoch, int n, uint8_t *ord) {
     for (int i = 0; i < n; ++i) ord[i] = (uint8_t)i;
+    if (n < 2) return;
+    int W = 0;
+    {
+        int wi = -1;
+        uint32_t prod = 1;
+        for (int i = n - 1; i >= 1; --i) {
+            const uint32_t m = (uint32_t)i + 1;
+            if (wi < 0 || (unsigned long long)prod * m > (1u << 22)) { ++wi; prod = 1; }
+            prod *= m;
+        }
+        W = wi + 1;
+    }
+    const int EPB = W <= 4 ? 4 / W : 1;
+    const uint64_t E = epoch / (uint64_t)EPB;
+    const int o = (int)(epoch % (uint64_t)EPB) * W;
     U4 x{0, 0, 0, 0};
-    int have = 0;
-    uint32_t blk = 0;
+    uint32_t r = 0, prod = 1;
+    int wi = -1, cur_blk = -1;
     for (int i = n - 1; i >= 1; --i) {
-        if ((have & 7) == 0) x = rng4(seed, ST_PERM, slot, (uint32_t)epoch, ((uint32_t)(epoch >> 32) << 8) | blk++);
-        const uint32_t word = word_of(x, (have & 7) >> 1);
-        const uint32_t chunk = (have & 1) ? (word >> 16) : (word & 0xFFFFu);
-        ++have;
-        const int j = (int)((chunk * (uint32_t)(i + 1)) >> 16);
+        const uint32_t m = (uint32_t)i + 1;
+        if (wi < 0 || (unsigned long long)prod * m > (1u << 22)) {
+            ++wi;
+            prod = 1;
+            const int g = o + wi, blk = g >> 2;
+            if (blk != cur_blk) {
+                x = rng4(seed, ST_PERM, slot, (uint32_t)E, ((uint32_t)(E >> 32) << 8) | (uint32_t)blk);
+                cur_blk = blk;
+            }
+            r = word_of(x, g & 3);
+        }
+        prod *= m;
+        const int j = (int)__umulhi(r, m);
+        r *= m;
         const uint8_t tmp = ord[i];
         ord[i] = ord[j];
         ord[j] = tmp;

@@ -76,6 +76,8 @@ class Soup(object):
             return False
         if len({b._desc.key() for b in bases}) != 1:
             return False
+        if len({float(b.get_params().get('epsilon')) for b in bases}) != 1:
+            return False      # the fused sweep tests every particle against one epsilon; the reference uses each particle's own
         if self._arena is None or self._arena.n != len(bases):
             self._arena = _eng.Population(bases[0]._desc, len(bases))
         for i, b in enumerate(bases):
@@ -154,6 +156,7 @@ class Soup(object):
                 fb = _base(fresh)
                 fb._release()
                 fb._pop = _eng.Population(fb._desc, 1, device=self._arena.device, ld=self._arena.ld, w=row)
+                fb._touch()      # later attackers of this sweep may already have rewritten the row: drop cached predicates
                 self.particles[i] = fresh
                 desc['action'] = 'divergent_dead' if action[i] == 4 else 'zweo_dead'
                 desc['counterpart'] = fresh.get_uid()
@@ -330,12 +333,14 @@ class PopulationSoup:
     so the result does not depend on how the population is sharded."""
 
     def __init__(self, kind, size, width=2, depth=2, aggregates=0, seed=0, group=None, device=None, backend=None,
-                 exchange="auto", order="snapshot", **params):
+                 exchange="auto", order="snapshot", sharded=True, **params):
         import torch
         import torch.distributed as dist
         self.desc = _eng.make_desc(kind, width, depth, aggregates)
         self.group = group
-        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        # sharded=False: this process owns the whole population even inside a process group (the single-owner twin the
+        # sharded result is checked against)
+        self.world = dist.get_world_size(group) if (sharded and dist.is_available() and dist.is_initialized()) else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
         self.size = int(size)
         self.slot0, self.n_local = shard_of(self.size, self.world, self.rank)
