@@ -119,16 +119,28 @@ int srnn_soup_ordered(const srnn_net_desc *d, const srnn_soup_params *p, float *
 
 /* Soup.evolve (code/soup.py:51-87) with the reference's EXACT sequential semantics at population scale: the result is
  * bit-identical to visiting the particles one by one in index order (= srnn_soup_ordered), but the generation runs
- * as a dependency-levelled wavefront of parallel rounds, in place on `w` (DESIGN.md "Soup modes").
+ * as a dependency-levelled wavefront, in place on `w` (DESIGN.md "Soup modes"): ONE cooperative launch whose CTAs meet
+ * at grid barriers; after the first pass only the not-yet-runnable events are revisited, and the device itself notices
+ * when none is left.
  *   att / lrn  int64[n] device arrays of target indices or -1 (host-drawn, e.g. Python `random` in the reference's
- *              order); both NULL = Philox draws of (seed, particle, gen), the same function srnn_soup_sync uses
- *   scratch    int32[7*n + 16], no initialisation needed
- *   action uint8[n], loss double[n], dead uint8[n] (all nullable); *rounds_out (HOST int, nullable) = rounds launched (a multiple of 4 >= the DAG depth)
- * Respawn = srnn_init(seed, slot, gen).  Unsharded soups only.  The call synchronises the stream once per batch of
- * 4 rounds (it reads the progress counter back), so unlike the other entry points it returns after the work is done. */
+ *              order); both NULL = Philox draws of (seed, particle, gen), the same function srnn_soup_sync uses;
+ *              exactly one of them NULL is an error
+ *   scratch    int32[SRNN_SOUP_EXACT_SCRATCH(n)], no initialisation needed
+ *   action uint8[n], loss double[n], dead uint8[n] (all nullable)
+ *   rounds_out (HOST int, nullable) = depth of the dependency DAG; asking for it makes the call wait for the stream
+ *              (one 4-byte read-back) -- pass NULL to stay asynchronous
+ * Respawn = srnn_init(seed, slot, gen).  Unsharded soups only; 3 n < 2^31. */
+#define SRNN_SOUP_EXACT_SCRATCH(n) (11 * (int64_t)(n) + ((int64_t)(n) + 1) / 2 + 64)
 int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, const int64_t *att,
                     const int64_t *lrn, uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss,
                     uint8_t *dead, int32_t *rounds_out, void *stream);
+
+/* n_gens exact-order generations (gen0, gen0 + 1, ...) with Philox pairings in ONE launch, fully asynchronous:
+ * the multi-generation form of Soup.evolve(iterations) (code/soup.py:51-53).  action / dead describe the LAST
+ * generation; rounds_dev (DEVICE int32[n_gens], nullable) receives every generation's DAG depth.  Same scratch. */
+int srnn_soup_exact_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, uint64_t seed,
+                        uint64_t gen0, int32_t n_gens, int32_t *scratch, uint8_t *action, uint8_t *dead,
+                        int32_t *rounds_dev, void *stream);
 
 /* Soup.evolve, snapshot-synchronous generation for large / sharded soups (DESIGN.md "Soup modes"): every
  * partner is read from `snap`, the start-of-generation arena of ALL n_total particles (after the

@@ -784,76 +784,57 @@ __global__ void soup_ordered_kernel(float *w, int64_t ld, int64_t n, const int64
 // Events that become ready in the same round cannot share a particle (the earlier one would be an unfinished
 // predecessor of the later one), so a round is one fully parallel kernel working in place on the arena; the number
 // of rounds is the depth of the dependency DAG (a few tens for random pairings).
-__global__ void __launch_bounds__(BS) soup_exact_lists_kernel(SoupP p, uint64_t seed, uint64_t gen, int64_t n,
-                                                              const int64_t *__restrict__ att_in,
-                                                              const int64_t *__restrict__ lrn_in, int32_t *att32,
-                                                              int32_t *lrn32, int32_t *headA, int32_t *nextA,
-                                                              int32_t *headL, int32_t *nextL) {
-    const int64_t i = (int64_t)blockIdx.x * BS + threadIdx.x;
-    if (i >= n) return;
-    int64_t a, l;
-    if (att_in) {
-        a = att_in[i];
-        l = lrn_in ? lrn_in[i] : -1;
-    } else {
-        soup_draw(p, seed, (uint64_t)i, gen, n, &a, &l);
-    }
-    att32[i] = (int32_t)a;
-    lrn32[i] = (int32_t)l;
-    if (a >= 0) nextA[i] = atomicExch(&headA[a], (int32_t)i);
-    if (l >= 0) nextL[i] = atomicExch(&headL[l], (int32_t)i);
-}
+// One cooperative launch runs whole generations: all CTAs are co-resident and meet at grid barriers between the phases
+//   P0 reset list heads / done flags   P1 draw pairings, thread events into the per-particle attacker / learner lists
+//   P2 every event finds its (<= 3) immediate predecessors; events with none run at once (round 0, ~2/3 of a soup at
+//      rates 0.1 / 0.1), the others go to a work list with their predecessors stored
+//   rounds: only the work list is visited -- ready events run, the rest are pushed to the next list -- until it is
+//      empty.  A round costs O(pending), the host never looks, the number of rounds is left in device memory.
+// Everything another CTA may have written earlier in the launch is read with L1-bypassing loads.
+#ifndef SRNN_EXACT_MINB
+#define SRNN_EXACT_MINB 3
+#endif
+struct ExactBufs {
+    int32_t *headA, *nextA, *headL, *nextL, *att32, *lrn32, *pred /* [3n] */, *wl[2] /* [n] each */;
+    uint16_t *stamp;     // [n] 0 = not run yet, else 1 + the round the event ran in
+    int32_t *cnt;        // [0..2] rotating work-list counters, [3] = rounds of the last generation, [4] = interacting particles
+    unsigned *barrier;
+};
 
-// the latest event before j that touches particle p (its own turn, an attack on it, a learn_from it), or -1
-__device__ __forceinline__ int32_t chain_pred(int32_t p, int32_t j, const int32_t *__restrict__ headA,
-                                              const int32_t *__restrict__ nextA, const int32_t *__restrict__ headL,
-                                              const int32_t *__restrict__ nextL) {
+__device__ __forceinline__ void grid_barrier(unsigned *counter, unsigned &target);
+
+// the latest event before j that touches particle p (its own turn, an attack on it, a learn_from it), or -1;
+// ha / hl = the already loaded list heads headA[p], headL[p]
+__device__ __forceinline__ int32_t chain_pred(int32_t p, int32_t j, int32_t ha, int32_t hl, const int32_t *nextA,
+                                              const int32_t *nextL) {
     int32_t best = p < j ? p : -1;
-    for (int32_t e = headA[p]; e >= 0; e = nextA[e])
+    for (int32_t e = ha; e >= 0; e = __ldcg(nextA + e))
         if (e < j && e > best) best = e;
-    for (int32_t e = headL[p]; e >= 0; e = nextL[e])
+    for (int32_t e = hl; e >= 0; e = __ldcg(nextL + e))
         if (e < j && e > best) best = e;
     return best;
 }
 
+__device__ __forceinline__ void warp_push(int32_t *counter, int32_t *list, int32_t value, bool pred);
+
+// particle j's turn, exactly as code/soup.py:55-87 (same body as the single-thread ordered kernel), in place
 template <class S>
-__global__ void __launch_bounds__(BS) soup_exact_round_kernel(float *w, int64_t ld, int64_t n, SoupP p, uint64_t seed,
-                                                              uint64_t gen, Limits lim, const int32_t *__restrict__ att32,
-                                                              const int32_t *__restrict__ lrn32,
-                                                              const int32_t *__restrict__ headA,
-                                                              const int32_t *__restrict__ nextA,
-                                                              const int32_t *__restrict__ headL,
-                                                              const int32_t *__restrict__ nextL,
-                                                              const uint8_t *__restrict__ done_prev, uint8_t *done_cur,
-                                                              uint8_t *action, double *loss, uint8_t *dead_out,
-                                                              unsigned long long *n_done) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    SgdScratch sc = sgd_scratch<S>(smem, BS);
-    __syncthreads();  // position codes visible
-    const int64_t j64 = (int64_t)blockIdx.x * BS + threadIdx.x;
-    if (j64 >= n) return;
-    const int32_t j = (int32_t)j64;
-    if (done_prev[j]) { done_cur[j] = 1; return; }
-    const int32_t a = att32[j], l = lrn32[j];
-    int32_t pr = chain_pred(j, j, headA, nextA, headL, nextL);
-    bool ready = pr < 0 || done_prev[pr];
-    if (ready && a >= 0 && a != j) { pr = chain_pred(a, j, headA, nextA, headL, nextL); ready = pr < 0 || done_prev[pr]; }
-    if (ready && l >= 0 && l != j && l != a) { pr = chain_pred(l, j, headA, nextA, headL, nextL); ready = pr < 0 || done_prev[pr]; }
-    if (!ready) { done_cur[j] = 0; return; }
-    // ---- particle j's turn, exactly as code/soup.py:55-87 (same body as the single-thread ordered kernel)
+__device__ __forceinline__ void exact_event(float *w, int64_t ld, int32_t j, int32_t a, int32_t l, const SoupP &p,
+                                            const SgdScratch &sc, uint64_t seed, uint64_t gen, const Limits &lim,
+                                            uint8_t *action, double *loss, uint8_t *dead_out, uint16_t *stamp,
+                                            uint16_t my_stamp, const float *preloaded = nullptr) {
     float cur[S::NW], oth[S::NW], res[S::NW];
     uint8_t act = SRNN_ACT_NONE;
     double ls = nan("");
     bool dead = false;
-    {
-        const float *rec = w + j64 * ld;
+    if (preloaded) {
 #pragma unroll
-        for (int k = 0; k < S::NW; ++k) cur[k] = rec[k];
+        for (int k = 0; k < S::NW; ++k) cur[k] = preloaded[k];
+    } else {
+        record_get<S::NW, LD_CG>(w + (int64_t)j * ld, cur);
     }
     if (a >= 0) {
-        const float *vr = w + (int64_t)a * ld;
-#pragma unroll
-        for (int k = 0; k < S::NW; ++k) oth[k] = vr[k];
+        record_get<S::NW, LD_CG>(w + (int64_t)a * ld, oth);
         net_apply<S>(cur, oth, res, sc.one);
         record_store<S::NW>(w, ld, a, res);
         if (a == j) {
@@ -864,17 +845,176 @@ __global__ void __launch_bounds__(BS) soup_exact_round_kernel(float *w, int64_t 
     }
     const bool has_teacher = l >= 0 && l != j, self_teacher = l == j;
     if (has_teacher) {
-        const float *tr = w + (int64_t)l * ld;   // plain load: the teacher may have been rewritten in an earlier round
+        float tch[S::NW];
+        record_get<S::NW, LD_CG>(w + (int64_t)l * ld, tch);
 #pragma unroll
-        for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tr[k];
+        for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tch[k];
     }
+    const bool touched = has_teacher || self_teacher || p.train > 0;
     soup_tail<S>(p, cur, sc, has_teacher, self_teacher, seed, (uint64_t)j, gen, lim, &act, &ls, nullptr, 0, 0, &dead);
-    record_store<S::NW>(w, ld, j64, cur);
+    if (touched || dead) record_store<S::NW>(w, ld, j, cur);   // an idle particle's record is left alone (a == j was stored above)
     if (action) action[j] = act;
     if (loss) loss[j] = ls;
     if (dead_out) dead_out[j] = dead ? 1 : 0;
-    done_cur[j] = 1;
-    atomicAdd(n_done, 1ull);
+    // No fence: a stamp only counts for readers of LATER rounds, and the grid barrier between rounds orders everything
+    // written before it (an event that sees a same-round stamp ignores it).
+    stamp[j] = my_stamp;
+}
+
+// One global atomic per CTA and loop iteration instead of one per warp: at 10 M particles the work-list counter is a
+// single L2 address, and 300 k returning atomics on it were the bottleneck of the streaming pass.  Must be reached by
+// every thread of the CTA (uniform loop bounds).
+__device__ __forceinline__ void block_push(int32_t *counter, int32_t *list, int32_t value, bool pred, int *s_cnt, int *s_base) {
+    if (threadIdx.x == 0) *s_cnt = 0;
+    __syncthreads();
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    const int lane = threadIdx.x & 31;
+    int wbase = 0;
+    if (m && lane == __ffs(m) - 1) wbase = atomicAdd(s_cnt, __popc(m));
+    wbase = __shfl_sync(0xffffffffu, wbase, m ? __ffs(m) - 1 : 0);
+    __syncthreads();
+    if (threadIdx.x == 0 && *s_cnt) *s_base = atomicAdd(counter, *s_cnt);
+    __syncthreads();
+    if (pred) list[*s_base + wbase + __popc(m & ((1u << lane) - 1u))] = value;
+}
+
+template <class S>
+__global__ void __launch_bounds__(BS, SRNN_EXACT_MINB) soup_exact_coop_kernel(float *w, int64_t ld, int64_t n, SoupP p, uint64_t seed,
+                                                             uint64_t gen0, int n_gens, Limits lim,
+                                                             const int64_t *__restrict__ att_in,
+                                                             const int64_t *__restrict__ lrn_in, ExactBufs b,
+                                                             uint8_t *action, double *loss, uint8_t *dead_out,
+                                                             int32_t *rounds_out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ __align__(16) float tile[BS * S::NW];
+    __shared__ int s_cnt, s_base;
+    SgdScratch sc = sgd_scratch<S>(smem, BS);
+    __syncthreads();  // position codes visible
+    unsigned target = 0;
+    const int64_t gtid = (int64_t)blockIdx.x * BS + threadIdx.x, gsize = (int64_t)gridDim.x * BS;
+    const int64_t cta0 = (int64_t)blockIdx.x * BS;     // CTA-uniform loop bounds wherever a block_push sits in the loop
+#ifdef SRNN_EXACT_TIMING
+    unsigned long long *tlog = reinterpret_cast<unsigned long long *>(b.barrier + 2);
+    int tl = 0;
+#define TSTAMP() do { if (gtid == 0 && tl < 24) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); tlog[tl++] = t_; } } while (0)
+#else
+#define TSTAMP() do { } while (0)
+#endif
+    for (int g = 0; g < n_gens; ++g) {
+        const uint64_t gen = gen0 + (uint64_t)g;
+#ifdef SRNN_EXACT_TIMING
+        tl = 0;
+#endif
+        TSTAMP();
+        // ---- P0
+        for (int64_t i = gtid; i < n; i += gsize) { b.headA[i] = -1; b.headL[i] = -1; b.stamp[i] = 0; }
+        if (gtid < 5 && gtid != 3) b.cnt[gtid] = 0;
+        grid_barrier(b.barrier, target);
+        TSTAMP();
+        // ---- P1
+        for (int64_t i = gtid; i < n; i += gsize) {
+            int64_t a, l;
+            if (att_in) { a = att_in[i]; l = lrn_in[i]; }
+            else soup_draw(p, seed, (uint64_t)i, gen, n, &a, &l);
+            b.att32[i] = (int32_t)a;
+            b.lrn32[i] = (int32_t)l;
+            if (a >= 0) b.nextA[i] = atomicExch(&b.headA[a], (int32_t)i);
+            if (l >= 0) b.nextL[i] = atomicExch(&b.headL[l], (int32_t)i);
+        }
+        grid_barrier(b.barrier, target);
+        TSTAMP();
+        // ---- P2a: streaming pass.  A particle nobody touches and that touches nobody (about 2/3 of a soup at rates 0.1 / 0.1)
+        //      has no predecessor: its turn runs here, with coalesced traffic only.  The others are compacted.
+        for (int64_t base = cta0; base < n; base += gsize) {
+            const int64_t j64 = base + threadIdx.x;
+            bool busy = false;
+            // the CTA's 256 records move as one contiguous, fully coalesced copy (per-thread record loads reach a third
+            // of the HBM bandwidth here: 56-byte records straddle the 16-byte vectors differently from lane to lane)
+            tile_stage_in<S::NW, BS, true>(w, ld, base, n, tile);
+            __syncthreads();
+            if (j64 < n) {
+                const int32_t j = (int32_t)j64;
+                float rec[S::NW];
+                tile_get<S::NW>(tile, threadIdx.x, rec);
+                const int32_t a = __ldcg(b.att32 + j), l = __ldcg(b.lrn32 + j), ha = __ldcg(b.headA + j), hl = __ldcg(b.headL + j);
+                if ((a & l & ha & hl) < 0)
+                    exact_event<S>(w, ld, j, -1, -1, p, sc, seed, gen, lim, action, loss, dead_out, b.stamp, (uint16_t)1, rec);
+                else busy = true;
+            }
+            block_push(&b.cnt[4], b.wl[1], (int32_t)j64, busy, &s_cnt, &s_base);
+        }
+        grid_barrier(b.barrier, target);
+        TSTAMP();
+        // ---- P2b: dense pass over the interacting particles: find the (<= 3) immediate predecessors of each event; events
+        //      without any run now (round 0), the others are listed with their predecessors
+        {
+            const int32_t mx = __ldcg(b.cnt + 4);
+            for (int64_t base = cta0; base < mx; base += gsize) {
+                const int64_t idx = base + threadIdx.x;
+                bool wait = false;
+                int32_t j = -1;
+                if (idx < mx) {
+                    j = __ldcg(b.wl[1] + idx);
+                    // the first-level loads are independent: issue them together
+                    const int32_t a = __ldcg(b.att32 + j), l = __ldcg(b.lrn32 + j), ha = __ldcg(b.headA + j), hl = __ldcg(b.headL + j);
+                    const bool va = a >= 0 && a != j, vl = l >= 0 && l != j && l != a;
+                    int32_t haa = -1, hla = -1, hal = -1, hll = -1;
+                    if (va) { haa = __ldcg(b.headA + a); hla = __ldcg(b.headL + a); }
+                    if (vl) { hal = __ldcg(b.headA + l); hll = __ldcg(b.headL + l); }
+                    const int32_t p0 = chain_pred(j, j, ha, hl, b.nextA, b.nextL);
+                    const int32_t p1 = va ? chain_pred(a, j, haa, hla, b.nextA, b.nextL) : -1;
+                    const int32_t p2 = vl ? chain_pred(l, j, hal, hll, b.nextA, b.nextL) : -1;
+                    if ((p0 & p1 & p2) < 0) {
+                        exact_event<S>(w, ld, j, a, l, p, sc, seed, gen, lim, action, loss, dead_out, b.stamp, (uint16_t)1);
+                    } else {
+                        b.pred[3 * (int64_t)j] = p0; b.pred[3 * (int64_t)j + 1] = p1; b.pred[3 * (int64_t)j + 2] = p2;
+                        wait = true;
+                    }
+                }
+                block_push(&b.cnt[0], b.wl[0], j, wait, &s_cnt, &s_base);
+            }
+        }
+        grid_barrier(b.barrier, target);
+        TSTAMP();
+        // ---- rounds over the pending events only
+        int rounds = 1;
+        for (int r = 0;; ++r, ++rounds) {
+            const int32_t m = __ldcg(b.cnt + r % 3);
+            if (m == 0) break;
+            if (gtid == 0) b.cnt[(r + 2) % 3] = 0;         // read in round r-1, pushed to in round r+1
+            const int32_t *src = b.wl[r & 1];
+            int32_t *dst = b.wl[(r + 1) & 1];
+            for (int64_t base = cta0; base < m; base += gsize) {
+                const int64_t idx = base + threadIdx.x;
+                bool wait = false;
+                int32_t j = -1;
+                if (idx < m) {
+                    j = __ldcg(src + idx);
+                    const int32_t p0 = __ldcg(b.pred + 3 * (int64_t)j), p1 = __ldcg(b.pred + 3 * (int64_t)j + 1),
+                                  p2 = __ldcg(b.pred + 3 * (int64_t)j + 2);
+                    const int32_t a = __ldcg(b.att32 + j), l = __ldcg(b.lrn32 + j);
+                    // a predecessor counts once it ran in an EARLIER round: stamp in 1 .. r + 1 (this round writes r + 2)
+                    const unsigned s0 = p0 < 0 ? 1u : __ldcg(b.stamp + p0), s1 = p1 < 0 ? 1u : __ldcg(b.stamp + p1),
+                                   s2 = p2 < 0 ? 1u : __ldcg(b.stamp + p2);
+                    const unsigned lim_stamp = (unsigned)r + 1u;
+                    if (s0 - 1u < lim_stamp && s1 - 1u < lim_stamp && s2 - 1u < lim_stamp) {
+                        exact_event<S>(w, ld, j, a, l, p, sc, seed, gen, lim, action, loss, dead_out, b.stamp,
+                                       (uint16_t)(r + 2));
+                    } else {
+                        wait = true;
+                    }
+                }
+                block_push(&b.cnt[(r + 1) % 3], dst, j, wait, &s_cnt, &s_base);
+            }
+            grid_barrier(b.barrier, target);
+            TSTAMP();
+            if (rounds >= 65000) break;                   // stamps are 16 bits: deeper chains are refused by the host check below
+        }
+        if (gtid == 0) {
+            b.cnt[3] = rounds;
+            if (rounds_out) rounds_out[g] = rounds;
+        }
+    }
 }
 
 // snapshot-synchronous, phase A: every owner evaluates the same pairing function for ALL global particles and
@@ -1902,56 +2042,72 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
                           shard_len, seed, gen, scratch, action, loss, dead, stream);
 }
 
-int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, const int64_t *att,
-                    const int64_t *lrn, uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss,
-                    uint8_t *dead, int32_t *rounds_out, void *stream) {
+// scratch layout (int32 words): headA[n] nextA[n] headL[n] nextL[n] att32[n] lrn32[n] pred[3n] wl0[n] wl1[n] stamp(n x 16 bit) cnt[4] barrier
+static int soup_exact_launch(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n,
+                             const int64_t *att, const int64_t *lrn, uint64_t seed, uint64_t gen0, int32_t n_gens,
+                             int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, int32_t *rounds_dev,
+                             int32_t **rounds_last, void *stream) {
     if (!d || !scratch) return fail(SRNN_ERR_ARG, "desc or scratch is NULL%s");
-    if (n <= 0) return n == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
-    if (n >= 0x7fffffffLL) return fail(SRNN_ERR_ARG, "need n < 2^31%s");
+    if (n_gens < 0) return fail(SRNN_ERR_ARG, "n_gens < 0%s");
+    if (n <= 0 || n_gens == 0) return n >= 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n < 0%s");
+    if (n >= 0x7fffffffLL / 3) return fail(SRNN_ERR_ARG, "need 3 n < 2^31%s");
     if ((att == nullptr) != (lrn == nullptr))
         return fail(SRNN_ERR_ARG, "srnn_soup_exact: pass both att and lrn (explicit pairings) or neither (Philox draws)%s");
+    if (att && n_gens != 1) return fail(SRNN_ERR_ARG, "explicit pairings describe ONE generation%s");
     SoupP q;
     int rc = make_soup(p, &q);
     if (rc) return rc;
-    const Limits lim = make_limits(d);
+    Limits lim = make_limits(d);
     cudaStream_t st = (cudaStream_t)stream;
-    int32_t *headA = scratch, *nextA = headA + n, *headL = nextA + n, *nextL = headL + n, *att32 = nextL + n,
-            *lrn32 = att32 + n;
-    uint8_t *done0 = reinterpret_cast<uint8_t *>(lrn32 + n), *done1 = done0 + n;
-    unsigned long long *n_done = reinterpret_cast<unsigned long long *>(scratch + 6 * n + (2 * n + 3) / 4 + 2);
-    n_done = reinterpret_cast<unsigned long long *>((reinterpret_cast<uintptr_t>(n_done) + 7) & ~uintptr_t(7));
-    cudaError_t ce = cudaMemsetAsync(headA, 0xFF, sizeof(int32_t) * (size_t)n, st);
-    if (ce == cudaSuccess) ce = cudaMemsetAsync(headL, 0xFF, sizeof(int32_t) * (size_t)n, st);
-    if (ce == cudaSuccess) ce = cudaMemsetAsync(done0, 0, (size_t)n, st);
-    if (ce == cudaSuccess) ce = cudaMemsetAsync(n_done, 0, sizeof(unsigned long long), st);
+    ExactBufs b;
+    b.headA = scratch; b.nextA = b.headA + n; b.headL = b.nextA + n; b.nextL = b.headL + n;
+    b.att32 = b.nextL + n; b.lrn32 = b.att32 + n; b.pred = b.lrn32 + n;
+    b.wl[0] = b.pred + 3 * n; b.wl[1] = b.wl[0] + n;
+    b.stamp = reinterpret_cast<uint16_t *>(b.wl[1] + n);
+    b.cnt = b.wl[1] + n + (n + 1) / 2;
+    b.barrier = reinterpret_cast<unsigned *>(b.cnt + 6);
+    if (rounds_last) *rounds_last = b.cnt + 3;
+    cudaError_t ce = cudaMemsetAsync(b.barrier, 0, sizeof(unsigned), st);
     if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
-    soup_exact_lists_kernel<<<grid_for(n), BS, 0, st>>>(q, seed, gen, n, att, lrn, att32, lrn32, headA, nextA, headL, nextL);
-    int rounds = 0;
-    unsigned long long done_host = 0;
-    // Rounds are launched in batches before the progress counter is read back (one host synchronisation per batch
-    // instead of per round); a round after completion only copies done flags, so overshooting is cheap.
-    const int batch = 4;
-    while (done_host < (unsigned long long)n) {
-        if (rounds >= 1 << 16) return fail(SRNN_ERR_LIMIT, "srnn_soup_exact: dependency chain deeper than 65536 rounds%s");
-        for (int b = 0; b < batch; ++b, ++rounds) {
-            const uint8_t *dp = (rounds & 1) ? done1 : done0;
-            uint8_t *dc = (rounds & 1) ? done0 : done1;
 #define BODY(S)                                                                                              \
     SRNN_CHECK_ARENA(w, ld, S)                                                                               \
     const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
-    rc = allow_smem(soup_exact_round_kernel<S>, sm);                                                         \
+    rc = allow_smem(soup_exact_coop_kernel<S>, sm);                                                          \
     if (rc) return rc;                                                                                       \
-    soup_exact_round_kernel<S><<<grid_for(n), BS, sm, st>>>(w, ld, n, q, seed, gen, lim, att32, lrn32, headA, nextA, headL, \
-                                                            nextL, dp, dc, action, loss, dead, n_done);
-            SRNN_DISPATCH(d)
+    int per_sm = 0, dev = 0, sms = 0;                                                                        \
+    cudaGetDevice(&dev);                                                                                     \
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);                                       \
+    ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, soup_exact_coop_kernel<S>, BS, sm);          \
+    if (ce != cudaSuccess || per_sm < 1) return fail(SRNN_ERR_CUDA, "occupancy query: %s", cudaGetErrorString(ce)); \
+    const unsigned grid = (unsigned)std::min<int64_t>((n + BS - 1) / BS, (int64_t)per_sm * sms);              \
+    void *args[] = {&w, &ld, &n, &q, &seed, &gen0, &n_gens, &lim, &att, &lrn, &b, &action, &loss, &dead, &rounds_dev}; \
+    ce = cudaLaunchCooperativeKernel((void *)soup_exact_coop_kernel<S>, dim3(grid), dim3(BS), args, sm, st);  \
+    if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cooperative launch: %s", cudaGetErrorString(ce));
+    SRNN_DISPATCH(d)
 #undef BODY
-        }
-        ce = cudaMemcpyAsync(&done_host, n_done, sizeof done_host, cudaMemcpyDeviceToHost, st);
-        if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
-        if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "srnn_soup_exact: %s", cudaGetErrorString(ce));
-    }
-    if (rounds_out) *rounds_out = rounds;
+    return check_launch("srnn_soup_exact");
+}
+
+int srnn_soup_exact(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, const int64_t *att,
+                    const int64_t *lrn, uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss,
+                    uint8_t *dead, int32_t *rounds_out, void *stream) {
+    int32_t *rounds_last = nullptr;
+    int rc = soup_exact_launch(d, p, w, ld, n, att, lrn, seed, gen, 1, scratch, action, loss, dead, nullptr, &rounds_last,
+                               stream);
+    if (rc || !rounds_out) return rc;
+    *rounds_out = 0;
+    if (n <= 0 || !rounds_last) return SRNN_OK;
+    cudaError_t ce = cudaMemcpyAsync(rounds_out, rounds_last, sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize((cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "srnn_soup_exact: %s", cudaGetErrorString(ce));
     return SRNN_OK;
+}
+
+int srnn_soup_exact_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w, int64_t ld, int64_t n, uint64_t seed,
+                        uint64_t gen0, int32_t n_gens, int32_t *scratch, uint8_t *action, uint8_t *dead,
+                        int32_t *rounds_dev, void *stream) {
+    return soup_exact_launch(d, p, w, ld, n, nullptr, nullptr, seed, gen0, n_gens, scratch, action, nullptr, dead,
+                             rounds_dev, nullptr, stream);
 }
 
 int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float *w_a, float *w_b, int64_t ld, int64_t n,

@@ -260,8 +260,9 @@ class _CudaBackend:
             warnings.warn("PopulationSoup: peer memory unavailable (%s); using the all-gather exchange" % (exc,))
             return None
 
-    def soup_exact(self, desc, sp_kwargs, w, seed, gen, scratch, action, dead):
-        return _eng.soup_exact(desc, _eng.make_soup_params(**sp_kwargs), w, seed, gen, scratch, action=action, dead=dead)
+    def soup_exact(self, desc, sp_kwargs, w, seed, gen0, n_gens, scratch, action, dead, rounds):
+        _eng.soup_exact_run(desc, _eng.make_soup_params(**sp_kwargs), w, seed, gen0, n_gens, scratch, action=action,
+                            dead=dead, rounds=rounds)
 
     def soup_sync_run(self, desc, sp_kwargs, w_a, w_b, seed, gen0, n_gens, scratch, action, dead):
         _eng.soup_sync_run(desc, _eng.make_soup_params(**sp_kwargs), w_a, w_b, seed, gen0, n_gens, scratch,
@@ -355,7 +356,7 @@ class PopulationSoup:
             raise ValueError("order must be 'snapshot' or 'exact'")
         if order == "exact" and self.world > 1:
             raise ValueError("exact-order generations are implemented for unsharded soups")
-        self.order, self.rounds = order, 0
+        self.order, self._rounds = order, None
         self.backend = backend or _CudaBackend(device)
         nw, B = self.desc.n_weights, self.backend
         # exchange of a sharded soup: "peer" = partner records are read straight from the owning GPU's arena over
@@ -376,7 +377,8 @@ class PopulationSoup:
             self.w = B.alloc((self.n_local, nw), torch.float32)
             self._next = B.alloc((self.n_local, nw), torch.float32)
             self._snap = B.alloc((self.size, nw), torch.float32) if self.world > 1 else None
-        self._scratch = B.alloc((max(_eng.soup_scratch_len(self.size, self.n_local), 7 * self.size + 16),), torch.int32)
+        words = _eng.soup_exact_scratch_len(self.size) if order == "exact" else _eng.soup_scratch_len(self.size, self.n_local)
+        self._scratch = B.alloc((words,), torch.int32)
         self.dead = B.alloc((self.n_local,), torch.uint8)
         self.action = B.alloc((self.n_local,), torch.uint8)
         self.uid = B.alloc((self.n_local,), torch.int64)
@@ -386,6 +388,11 @@ class PopulationSoup:
         self.next_uid = self.size
         self.track_uids = False
         self._watch = None          # (local indices, every, {local index -> list of state dicts})
+
+    @property
+    def rounds(self):
+        """Depth of the dependency DAG of the last exact-order generation (reads one int back from the device)."""
+        return 0 if self._rounds is None else int(self._rounds[-1].item())
 
     @property
     def local(self):
@@ -411,9 +418,18 @@ class PopulationSoup:
         import torch.distributed as dist
         sp, B = self._sp(), self.backend
         if self.order == "exact":
-            for _ in range(iterations):
-                self.time += 1
-                self.rounds = B.soup_exact(self.desc, sp, self.w, self.seed, self.time, self._scratch, self.action, self.dead)
+            # the reference's sequential sweep as a wavefront: whole generations in one cooperative launch, no host sync;
+            # uid tracking / watching need the host between generations, so they go one generation per launch
+            import torch
+            step = 1 if (self.track_uids or self._watch is not None) else iterations
+            done = 0
+            while done < iterations:
+                k = min(step, iterations - done)
+                self._rounds = B.alloc((k,), torch.int32) if hasattr(B, "alloc") else None
+                B.soup_exact(self.desc, sp, self.w, self.seed, self.time + 1, k, self._scratch, self.action, self.dead,
+                             self._rounds)
+                self.time += k
+                done += k
                 if self.track_uids:
                     self._assign_uids()
                 self._log_watched()

@@ -28,7 +28,7 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_exact_run", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
 UIDS_STATIC_MAX = 1 << 24
 
 
@@ -294,6 +294,19 @@ def soup_exact(desc, params, w, seed, gen, scratch, att=None, lrn=None, action=N
                                _ptr(att), _ptr(lrn), C.c_uint64(seed), C.c_uint64(gen), _ptr(scratch), _ptr(action),
                                _ptr(loss), _ptr(dead), C.byref(rounds), _stream()))
     return rounds.value
+
+
+def soup_exact_scratch_len(n):
+    """int32 words of scratch srnn_soup_exact / srnn_soup_exact_run need (SRNN_SOUP_EXACT_SCRATCH in the header)."""
+    return 11 * int(n) + (int(n) + 1) // 2 + 64
+
+
+def soup_exact_run(desc, params, w, seed, gen0, n_gens, scratch, action=None, dead=None, rounds=None):
+    """n_gens exact-order generations with Philox pairings in ONE asynchronous cooperative launch (in place on w).
+    rounds: optional int32 device tensor [n_gens] receiving each generation's dependency depth."""
+    _chk(lib().srnn_soup_exact_run(C.byref(desc), C.byref(params), _ptr(w), C.c_int64(w.shape[1]), C.c_int64(w.shape[0]),
+                                   C.c_uint64(seed), C.c_uint64(gen0), C.c_int32(n_gens), _ptr(scratch), _ptr(action),
+                                   _ptr(dead), _ptr(rounds), _stream()))
 
 
 def soup_sync_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action=None, loss=None,
