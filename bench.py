@@ -311,7 +311,7 @@ def secondary_legs(eng, torch, dist, rank, world, dev, probe):
     kw = dict(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, epsilon=1e-4)
     kinds = ((eng.KIND_WW, 0), (eng.KIND_AGG, 4), (eng.KIND_RNN, 0))
     gens, res, host = 20, {}, {}
-    for exchange in (("allgather", "auto") if world > 1 else ("auto",)):
+    for exchange in (("allgather", "peer_unchained", "peer") if world > 1 else ("auto",)):
         soups = [PopulationSoup(k, third, aggregates=a, seed=5 + k, exchange=exchange, **kw).seed_particles()
                  for k, a in kinds]
         evolve_together(soups, 2)

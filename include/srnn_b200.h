@@ -167,6 +167,32 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
                          int64_t shard_len, int32_t my_shard, int64_t ld, float *w_out, int64_t out_ld, uint64_t seed,
                          uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead, void *stream);
 
+/* The same generation of a sharded soup as srnn_soup_sync_peers, with the attack lists built by the ATTACKER's rank
+ * (no counterpart in the reference: code/soup.py:56-61 is one process; this is what keeps the per-generation cost of a
+ * rank proportional to ITS particles).  Every rank holds, in peer-mapped memory, two parities of
+ *     head  int32[shard_len]   last attacker pushed onto each of ITS particles, -1 = none
+ *     next  int32[n_total]     previous head, stored by attacker g at index g
+ * heads_cur / nexts_cur (HOST arrays of n_shards device pointers) are the arrays that hold THIS generation's lists (only
+ * [my_shard] is read, and its heads are reset to -1 as they are consumed); heads_nxt / nexts_nxt (both NULL: skip)
+ * are the other parity: the kernel pushes generation gen+1's attacks of this rank's particles onto the victim owners'
+ * lists -- one system-scope exchange + one store over NVLink per attack.  Protocol: all heads -1, barrier across ranks,
+ * srnn_soup_push_lists(gen0) on every rank, barrier, then per generation: this call, barrier, swap parities and arenas.
+ * The per-generation barrier can be left to the library: flags (HOST array of n_shards device pointers, nullable) points
+ * at every rank's int32[n_shards + 1] flag array in peer-mapped memory (zeroed once, before the first generation and
+ * behind a barrier).  Behind the generation a one-warp kernel stores gen into word my_shard of every rank's array;
+ * wait_gen > 0 makes the call wait -- on the device, ahead of the generation -- until this rank's array shows every
+ * rank at wait_gen or later (pass gen - 1 from the second generation of a run on; generations count up, < 2^31). */
+int srnn_soup_chain_peers(const srnn_net_desc *d, const srnn_soup_params *p, const float *const *shards, int32_t n_shards,
+                          int64_t shard_len, int32_t my_shard, int64_t ld, float *w_out, int64_t out_ld, uint64_t seed,
+                          uint64_t gen, int32_t *const *heads_cur, int32_t *const *nexts_cur, int32_t *const *heads_nxt,
+                          int32_t *const *nexts_nxt, int32_t *const *flags, int64_t wait_gen, uint8_t *action, double *loss,
+                          uint8_t *dead, void *stream);
+
+/* First generation of such a run: this rank's particles push their generation-`gen` attacks (Philox draws of
+ * (seed, global particle, gen), code/soup.py:56-59) onto the owners' lists.  heads must be -1 on every rank beforehand. */
+int srnn_soup_push_lists(const srnn_soup_params *p, int32_t n_shards, int64_t shard_len, int32_t my_shard, uint64_t seed,
+                         uint64_t gen, int32_t *const *heads, int32_t *const *nexts, void *stream);
+
 /* n_gens consecutive snapshot-synchronous generations (gen0, gen0+1, ...) of an UNSHARDED soup in one call, so a
  * small soup is not bound by the host's per-call overhead: generation gen0+g reads w_a and writes w_b for even g,
  * the other way round for odd g -- the newest arena is w_b if n_gens is odd, else w_a.  Same arguments and

@@ -1311,6 +1311,97 @@ __global__ void __launch_bounds__(SBS, MB) soup_chain_kernel(const float *__rest
     }
 }
 
+// ---- sharded soups: the attack lists are built by the ATTACKER's owner.  head / next of every rank live in peer-mapped
+// memory (head[r]: one word per particle of rank r; next[r]: one word per GLOBAL particle); an attacker pushes itself
+// onto its victim's list with one system-scope exchange on the victim owner's head word and stores the previous head
+// into the owner's next[] at its own global index.  Generation g's kernel pushes generation g+1's events (other
+// parity of the list arrays), so a generation is ONE launch per rank whose cost is proportional to the rank's own
+// particles: no pass over all n_total particles, no memset.
+struct PeerListTable {
+    int32_t *head[SRNN_MAX_SHARDS];
+    int32_t *next[SRNN_MAX_SHARDS];
+};
+// flag[r] = rank r's int32[n + 1] in peer-mapped memory: word s = last generation rank s completed, word n = scratch
+struct PeerFlagTable {
+    int32_t *flag[SRNN_MAX_SHARDS];
+    int32_t n;       // 0: no fused signalling
+};
+__device__ __forceinline__ void push_attack(const SoupP &p, uint64_t seed, int64_t g, uint64_t gen, int64_t n_total,
+                                            int64_t shard_len, const PeerListTable &t) {
+    int64_t at, lr;
+    soup_draw(p, seed, (uint64_t)g, gen, n_total, &at, &lr);
+    if (at >= 0) {
+        const uint32_t r = (uint32_t)at / (uint32_t)shard_len;        // n_total < 2^31
+        const int64_t v = at - (int64_t)r * shard_len;
+        const int32_t old = atomicExch_system(t.head[r] + v, (int32_t)g);
+        t.next[r][g] = old;
+    }
+}
+template <class S, int SBS, int MB>
+__global__ void __launch_bounds__(SBS, MB) soup_chain_peers_kernel(ShardTable snap, const float *__restrict__ own,
+                                                                   int64_t ld, int64_t n_total, float *__restrict__ w_out,
+                                                                   int64_t out_ld, int64_t slot0, int64_t n, SoupP p,
+                                                                   uint64_t seed, uint64_t gen, Limits lim, int32_t *head_cur,
+                                                                   const int32_t *next_cur, PeerListTable nxt, int make_next,
+                                                                   uint8_t *action, double *loss, uint8_t *dead_out) {
+    // Generation g+1's pushes go FIRST: the exchange on the victim owner's head word is a round trip over NVLink, and
+    // issued here it travels under the whole tile generation instead of holding the finished CTA on the SM (at the tail
+    // it cost 15 % at 2 GPUs).  Only the returned previous head has to be kept until the store below.
+    constexpr int PPT = soup_ppt<S>();
+    int32_t old[PPT];
+    int32_t *slot[PPT];
+#pragma unroll
+    for (int r = 0; r < PPT; ++r) {
+        const int64_t i = (int64_t)blockIdx.x * soup_tile<S>() + threadIdx.x + r * SBS;
+        slot[r] = nullptr;
+        old[r] = -1;
+        if (i < n && make_next && p.attacking_rate > 0.0) {
+            int64_t at, lr;
+            soup_draw(p, seed, (uint64_t)(slot0 + i), gen + 1, n_total, &at, &lr);
+            if (at >= 0) {
+                const uint32_t rk = (uint32_t)at / (uint32_t)snap.len;        // n_total < 2^31
+                old[r] = atomicExch_system(nxt.head[rk] + (at - (int64_t)rk * snap.len), (int32_t)(slot0 + i));
+                slot[r] = nxt.next[rk] + (slot0 + i);
+            }
+        }
+    }
+    soup_tile_generation<S, SBS, false, soup_qdiv(MB)>(blockIdx.x, snap, own, ld, n_total, w_out, out_ld, slot0, n, p, seed, gen,
+                                                       lim, head_cur, next_cur, action, loss, dead_out);
+#pragma unroll
+    for (int r = 0; r < PPT; ++r) {
+        const int64_t i = (int64_t)blockIdx.x * soup_tile<S>() + threadIdx.x + r * SBS;
+        if (i < n) head_cur[i] = -1;   // only this CTA reads its heads, and it is done with them; pushes for g+2 come after a barrier
+        if (slot[r]) *slot[r] = old[r];
+    }
+}
+// ---- cross-GPU ordering without a host-side barrier: after the generation kernel a one-warp kernel stores `gen` into
+// word my_shard of every rank's flag array (the kernel boundary in front of it makes the generation's records, pushes
+// and head resets visible system-wide; a per-CTA __threadfence_system() inside the generation kernel was measured 30 %
+// slower at 2 GPUs), and in front of the next generation a one-warp kernel waits for every rank's flag.
+__global__ void soup_signal_flags_kernel(PeerFlagTable flags, int my_shard, int32_t gen) {
+    const int r = threadIdx.x;
+    if (r < flags.n) {
+        __threadfence_system();
+        *reinterpret_cast<volatile int32_t *>(flags.flag[r] + my_shard) = gen;
+    }
+}
+// A kernel of its own rather than a spin at the top of the generation kernel: that would park a GPU-full of CTAs, and
+// with several soups per GPU (the kinds of a mixed soup on their streams) parked CTAs of one kind could starve the kind
+// the peers are waiting for.
+__global__ void soup_wait_flags_kernel(const int32_t *my_flags, int n_shards, int32_t want) {
+    const int r = threadIdx.x;
+    if (r < n_shards) {
+        while (*reinterpret_cast<const volatile int32_t *>(my_flags + r) < want) { }
+        __threadfence_system();
+    }
+}
+// the lists of the FIRST generation of a run: every rank pushes the attacks of its own particles
+__global__ void __launch_bounds__(BS) soup_push_lists_kernel(SoupP p, uint64_t seed, uint64_t gen, int64_t n_total,
+                                                             int64_t shard_len, int64_t slot0, PeerListTable t) {
+    const int64_t i = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (i < shard_len) push_attack(p, seed, slot0 + i, gen, n_total, shard_len, t);
+}
+
 // Persistent variant for small, launch-bound soups (one GPU, whole population): the generation loop runs ON the device.
 // All CTAs are co-resident (cooperative launch) and meet at a grid barrier twice per generation:
 //   [pairing draws -> attack lists]  barrier  [tile generations, reset own list heads]  barrier
@@ -2040,6 +2131,101 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
     tab.n = n_shards;
     return soup_sync_impl(d, p, tab, shards[my_shard], ld, shard_len * n_shards, w_out, out_ld, (int64_t)my_shard * shard_len,
                           shard_len, seed, gen, scratch, action, loss, dead, stream);
+}
+
+static int fill_list_table(PeerListTable *t, int32_t *const *heads, int32_t *const *nexts, int32_t n_shards) {
+    memset(t, 0, sizeof *t);
+    for (int r = 0; r < n_shards; ++r) {
+        if (!heads[r] || !nexts[r]) return fail(SRNN_ERR_ARG, "a list pointer is NULL%s");
+        t->head[r] = heads[r];
+        t->next[r] = nexts[r];
+    }
+    return SRNN_OK;
+}
+
+int srnn_soup_push_lists(const srnn_soup_params *p, int32_t n_shards, int64_t shard_len, int32_t my_shard, uint64_t seed,
+                         uint64_t gen, int32_t *const *heads, int32_t *const *nexts, void *stream) {
+    if (!heads || !nexts) return fail(SRNN_ERR_ARG, "heads or nexts is NULL%s");
+    if (n_shards < 1 || n_shards > SRNN_MAX_SHARDS || my_shard < 0 || my_shard >= n_shards)
+        return fail(SRNN_ERR_ARG, "need 1 <= n_shards <= SRNN_MAX_SHARDS and 0 <= my_shard < n_shards%s");
+    if (shard_len <= 0) return shard_len == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "shard_len < 0%s");
+    if (shard_len * n_shards >= 0x7fffffffLL) return fail(SRNN_ERR_ARG, "need n_total < 2^31%s");
+    SoupP q;
+    int rc = make_soup(p, &q);
+    if (rc) return rc;
+    PeerListTable t;
+    rc = fill_list_table(&t, heads, nexts, n_shards);
+    if (rc) return rc;
+    if (q.attacking_rate > 0.0)
+        soup_push_lists_kernel<<<grid_for(shard_len), BS, 0, (cudaStream_t)stream>>>(q, seed, gen, shard_len * n_shards, shard_len,
+                                                                                     (int64_t)my_shard * shard_len, t);
+    return check_launch("srnn_soup_push_lists");
+}
+
+int srnn_soup_chain_peers(const srnn_net_desc *d, const srnn_soup_params *p, const float *const *shards, int32_t n_shards,
+                          int64_t shard_len, int32_t my_shard, int64_t ld, float *w_out, int64_t out_ld, uint64_t seed,
+                          uint64_t gen, int32_t *const *heads_cur, int32_t *const *nexts_cur, int32_t *const *heads_nxt,
+                          int32_t *const *nexts_nxt, int32_t *const *flags, int64_t wait_gen, uint8_t *action, double *loss,
+                          uint8_t *dead, void *stream) {
+    if (!d || !shards || !w_out || !heads_cur || !nexts_cur) return fail(SRNN_ERR_ARG, "a required pointer is NULL%s");
+    if (gen >= 0x7fffffffULL && flags) return fail(SRNN_ERR_ARG, "fused signalling needs gen < 2^31%s");
+    if (n_shards < 1 || n_shards > SRNN_MAX_SHARDS || my_shard < 0 || my_shard >= n_shards)
+        return fail(SRNN_ERR_ARG, "need 1 <= n_shards <= SRNN_MAX_SHARDS and 0 <= my_shard < n_shards%s");
+    if (shard_len <= 0) return shard_len == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "shard_len < 0%s");
+    const int64_t n_total = shard_len * n_shards, n = shard_len, slot0 = (int64_t)my_shard * shard_len;
+    if (n_total >= 0x7fffffffLL) return fail(SRNN_ERR_ARG, "need n_total < 2^31%s");
+    if ((heads_nxt == nullptr) != (nexts_nxt == nullptr)) return fail(SRNN_ERR_ARG, "pass both heads_nxt and nexts_nxt or neither%s");
+    ShardTable tab;
+    memset(&tab, 0, sizeof tab);
+    for (int r = 0; r < n_shards; ++r) {
+        if (!shards[r]) return fail(SRNN_ERR_ARG, "a shard pointer is NULL%s");
+        if (ranges_overlap(w_out, shard_len, out_ld, shards[r], shard_len, ld))
+            return fail(SRNN_ERR_ARG, "w_out must not overlap a shard%s");
+        tab.base[r] = shards[r];
+    }
+    tab.len = shard_len;
+    tab.n = n_shards;
+    if (!heads_cur[my_shard] || !nexts_cur[my_shard]) return fail(SRNN_ERR_ARG, "this rank's list pointers are NULL%s");
+    SoupP q;
+    int rc = make_soup(p, &q);
+    if (rc) return rc;
+    const Limits lim = make_limits(d);
+    PeerListTable nxt;
+    memset(&nxt, 0, sizeof nxt);
+    const int make_next = heads_nxt != nullptr;
+    if (make_next) {
+        rc = fill_list_table(&nxt, heads_nxt, nexts_nxt, n_shards);
+        if (rc) return rc;
+    }
+    int32_t *head_cur = heads_cur[my_shard];
+    const int32_t *next_cur = nexts_cur[my_shard];
+    const float *own = shards[my_shard];
+    PeerFlagTable ft;
+    memset(&ft, 0, sizeof ft);
+    if (flags) {
+        for (int r = 0; r < n_shards; ++r) {
+            if (!flags[r]) return fail(SRNN_ERR_ARG, "a flag pointer is NULL%s");
+            ft.flag[r] = flags[r];
+        }
+        ft.n = n_shards;
+        if (wait_gen > 0)
+            soup_wait_flags_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(flags[my_shard], n_shards, (int32_t)wait_gen);
+    }
+#define BODY(S)                                                                                              \
+    if (ld < S::NW || out_ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s"); \
+    constexpr int SBS = SOUP_BS;                                                                             \
+    const size_t sm = sgd_smem_bytes<S>(SBS);                                                                \
+    const unsigned grid = (unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>());                             \
+    if (n >= SOUP_DENSE_MIN)                                                                                 \
+        soup_chain_peers_kernel<S, SBS, SRNN_SOUP_MINB><<<grid, SBS, sm, (cudaStream_t)stream>>>(            \
+            tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, nxt, make_next, action, loss, dead); \
+    else                                                                                                     \
+        soup_chain_peers_kernel<S, SBS, SOUP_MINB_SMALL><<<grid, SBS, sm, (cudaStream_t)stream>>>(           \
+            tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, nxt, make_next, action, loss, dead);
+    SRNN_DISPATCH(d)
+#undef BODY
+    if (ft.n > 0) soup_signal_flags_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ft, my_shard, (int32_t)gen);
+    return check_launch("srnn_soup_chain_peers");
 }
 
 // scratch layout (int32 words): headA[n] nextA[n] headL[n] nextL[n] att32[n] lrn32[n] pred[3n] wl0[n] wl1[n] stamp(n x 16 bit) cnt[4] barrier

@@ -260,6 +260,30 @@ class _CudaBackend:
             warnings.warn("PopulationSoup: peer memory unavailable (%s); using the all-gather exchange" % (exc,))
             return None
 
+    def peer_lists(self, n_local, n_total, group):
+        """Attack-list arrays in peer-mapped memory: (2 parities) x (head[n_local] | next[n_total]) int32 per rank,
+        followed by 64 words for the generation flags of the fused cross-GPU signal; returns (tensor, handle) or None."""
+        try:
+            import torch
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm
+            buf = symm.empty((2 * (n_local + n_total) + 64,), dtype=torch.int32, device=self.device)
+            hdl = symm.rendezvous(buf, group if group is not None else dist.group.WORLD)
+            if len(hdl.buffer_ptrs) != hdl.world_size or any(int(q) == 0 for q in hdl.buffer_ptrs):
+                return None
+            buf.fill_(-1)
+            return buf, hdl
+        except Exception:
+            return None
+
+    def soup_push_lists(self, sp, n_shards, shard_len, my_shard, seed, gen, heads, nexts, stream=None):
+        _eng.soup_push_lists(sp, n_shards, shard_len, my_shard, seed, gen, heads, nexts, stream=stream)
+
+    def soup_chain_peers(self, desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur,
+                         heads_nxt, nexts_nxt, action, dead, stream=None, flags=None, wait_gen=0):
+        _eng.soup_chain_peers(desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur,
+                              heads_nxt, nexts_nxt, action=action, dead=dead, stream=stream, flags=flags, wait_gen=wait_gen)
+
     def soup_exact(self, desc, sp_kwargs, w, seed, gen0, n_gens, scratch, action, dead, rounds):
         _eng.soup_exact_run(desc, _eng.make_soup_params(**sp_kwargs), w, seed, gen0, n_gens, scratch, action=action,
                             dead=dead, rounds=rounds)
@@ -295,12 +319,12 @@ _SIDE_STREAMS = {}
 def evolve_together(soups, iterations=1):
     """Advance several PopulationSoups in lock step -- the kinds of a mixed soup (separate arenas, partners within
     kind).  Results equal `for s in soups: s.evolve(iterations)` bit for bit: the soups do not
-    interact.  For sharded soups with the peer-memory exchange the kinds' generation kernels go to separate streams
-    (they are small and latency-bound at 8 GPUs: three of them fill the SMs together) and the ranks meet at ONE
-    cross-GPU barrier per generation instead of one per kind; anything else falls back to the plain loop."""
+    interact.  For sharded soups with the peer-memory exchange every kind runs its own chain of generations and
+    cross-GPU barriers on its own stream (they are small and latency-bound at 8 GPUs: three of them fill the SMs
+    together, and nobody waits for another kind's barrier); anything else falls back to the plain loop."""
     soups = list(soups)
     fast = len(soups) > 1 and all(isinstance(s, PopulationSoup) and s._peer is not None and s.order == "snapshot"
-                                  for s in soups)
+                                  for s in soups) and len({s._lists is None for s in soups}) == 1
     if not fast:
         for s in soups:
             s.evolve(iterations)
@@ -310,19 +334,38 @@ def evolve_together(soups, iterations=1):
     side = _SIDE_STREAMS.setdefault((dev.index, len(soups)), [torch.cuda.Stream(device=dev) for _ in soups])
     main = torch.cuda.current_stream(dev)
     sps = [_eng.make_soup_params(**s._sp()) if isinstance(s.backend, _CudaBackend) else s._sp() for s in soups]
-    fork, joins = torch.cuda.Event(), [torch.cuda.Event() for _ in soups]
     barrier = soups[0]._peer[1].barrier
-    for _ in range(iterations):
-        fork.record(main)
-        for s, sp, st, ev in zip(soups, sps, side, joins):
-            s.time += 1
-            st.wait_event(fork)
-            s._peer_generation(sp, stream=st)
-            ev.record(st)
-            main.wait_event(ev)
-        barrier()                         # one barrier orders every kind's reads of generation g on every rank
+    if iterations > 0 and any(s._chain_stale() for s in soups):
+        barrier()                         # nobody is still pushing into anybody's lists
         for s in soups:
-            s._peer_flip()
+            s._chain_reset()
+        barrier()                         # every rank's heads are reset before anybody pushes
+        for s, sp in zip(soups, sps):
+            s._chain_push_first(sp)
+        barrier()                         # the first generation's lists are complete on every rank
+    # Each kind runs its own chain  generation -> cross-GPU barrier -> generation ...  on its own stream, with its own
+    # symmetric-memory handle: the kinds never wait for each other, so one kind's barrier (a round trip over NVLink)
+    # travels under the other kinds' kernels instead of idling the GPU once per generation.
+    fork = torch.cuda.Event()
+    fork.record(main)
+    for st in side:
+        st.wait_event(fork)
+    for _ in range(iterations):           # enqueued generation by generation so that all chains start at once
+        for s, sp, st in zip(soups, sps, side):
+            if s._lists is not None and not s.track_uids and s._watch is None:
+                s.time += 1               # chained exchange: one C call on an explicit stream, nothing else to order
+                s._peer_generation(sp, stream=st)
+                s._peer_flip()
+                continue
+            with torch.cuda.stream(st):
+                s.time += 1
+                if not s._peer_generation(sp, stream=st):
+                    s._peer[1].barrier()  # all ranks finished this kind's generation g before anyone overwrites it
+                s._peer_flip()
+    for st in side:
+        join = torch.cuda.Event()
+        join.record(st)
+        main.wait_event(join)
     return soups
 
 
@@ -363,12 +406,23 @@ class PopulationSoup:
         # NVLink inside the generation kernel (srnn_soup_sync_peers); "allgather" = NCCL all-gather of the arenas,
         # then srnn_soup_sync; "auto" = peer when symmetric memory can be set up
         self._peer = None
-        if self.world > 1 and exchange in ("auto", "peer") and hasattr(B, "peer_arena"):
+        if self.world > 1 and exchange in ("auto", "peer", "peer_unchained") and hasattr(B, "peer_arena"):
             self._peer = B.peer_arena(self.n_local, nw, group)
-            if self._peer is None and exchange == "peer":
+            if self._peer is None and exchange != "auto":
                 raise RuntimeError("peer-memory exchange requested but symmetric memory is unavailable")
-        self.exchange = "peer" if self._peer is not None else ("allgather" if self.world > 1 else "none")
+        # "peer": attack lists built by the attackers' ranks, one launch per generation (srnn_soup_chain_peers);
+        # "peer_unchained": every rank re-draws all pairings and builds its lists locally (srnn_soup_sync_peers)
+        # "auto" picks by measurement (mixed 10 M soup, generations/s, unchained vs chained): 2 GPUs 2020 vs 1792,
+        # 4 GPUs 3263 vs 3147, 8 GPUs 5534 vs 5716 -- the chained form wins once the all-particle list pass dominates
+        unchained = exchange == "peer_unchained" or (exchange == "auto" and self.world <= 4)
+        self.exchange = ("peer_unchained" if unchained else "peer") if self._peer is not None else (
+            "allgather" if self.world > 1 else "none")
         self._shard_arrays = None
+        self._lists = None          # chained peer exchange: attack lists in peer memory, built by the attackers' ranks
+        self._lists_valid = None    # (generation, parameters) the lists of parity generation & 1 were built for
+        if self._peer is not None and hasattr(B, "peer_lists") and self.params.get("engine_path", 0) == 0 \
+                and self.exchange == "peer":
+            self._lists = B.peer_lists(self.n_local, self.size, group)
         if self._peer is not None:
             buf, _ = self._peer
             self._cur = 0
@@ -442,11 +496,18 @@ class PopulationSoup:
             if iterations & 1:
                 self.w, self._next = self._next, self.w
             return self
+        if self._peer is not None and iterations > 0 and self._chain_stale():
+            spc = _eng.make_soup_params(**sp) if isinstance(B, _CudaBackend) else sp
+            self._peer[1].barrier()
+            self._chain_reset()
+            self._peer[1].barrier()
+            self._chain_push_first(spc)
+            self._peer[1].barrier()
         for _ in range(iterations):
             self.time += 1
             if self._peer is not None:
-                self._peer_generation(sp)
-                self._peer[1].barrier()      # all ranks finished reading generation g before anyone overwrites it
+                if not self._peer_generation(sp):
+                    self._peer[1].barrier()  # all ranks finished reading generation g before anyone overwrites it
                 self._peer_flip()
                 continue
             if self.world > 1:
@@ -462,15 +523,69 @@ class PopulationSoup:
             self._log_watched()
         return self
 
+    def _list_tables(self):
+        """Pointer tables of every rank's list arrays: [parity] -> (heads, nexts); [2] = the flag arrays."""
+        if getattr(self, "_list_ptrs", None) is None:
+            stride = (self.n_local + self.size) * 4
+            self._list_ptrs = []
+            for par in (0, 1):
+                heads = _eng.shard_ptr_array([int(q) + par * stride for q in self._lists[1].buffer_ptrs])
+                nexts = _eng.shard_ptr_array([int(q) + par * stride + self.n_local * 4 for q in self._lists[1].buffer_ptrs])
+                self._list_ptrs.append((heads, nexts))
+            self._list_ptrs.append(_eng.shard_ptr_array([int(q) + 2 * stride for q in self._lists[1].buffer_ptrs]))
+        return self._list_ptrs
+
+    def _params_key(self):
+        return tuple(sorted((k, float(v) if isinstance(v, float) else v) for k, v in self._sp().items()))
+
+    def _chain_stale(self):
+        """True when the lists of generation time+1 still have to be built (first run, parameters changed, or the soup
+        was advanced some other way).  Every rank takes the same decision.  The caller then runs the bootstrap:
+        barrier, _chain_reset, barrier, _chain_push_first, barrier."""
+        return self._lists is not None and self._lists_valid != (self.time + 1, self._params_key())
+
+    def _chain_reset(self):
+        if self._lists is None or not self._chain_stale():
+            return
+        per = self.n_local + self.size
+        buf = self._lists[0]
+        buf[:self.n_local].fill_(-1)
+        buf[per:per + self.n_local].fill_(-1)
+        flags = buf[2 * per:2 * per + 64]
+        flags.fill_(self.time)               # "every rank has completed generation `time`"
+        flags[self.world] = 0                # the CTA counter of the fused signal
+        self._lists_valid = None
+
+    def _chain_push_first(self, sp):
+        if self._lists is None or self._lists_valid is not None:
+            return
+        heads, nexts = self._list_tables()[(self.time + 1) & 1]
+        self.backend.soup_push_lists(sp, self.world, self.n_local, self.rank, self.seed, self.time + 1, heads, nexts)
+        self._lists_valid = (self.time + 1, self._params_key())
+
     def _peer_generation(self, sp, stream=None):
-        """Launch generation self.time of a peer-exchange soup (no cross-GPU barrier) on `stream` / the current stream."""
+        """Launch generation self.time of a peer-exchange soup on `stream` / the current stream.  Returns True when the
+        launch carries its own cross-GPU ordering (chained exchange: generation flags), False when the caller still
+        has to barrier before the next generation."""
         if self._shard_arrays is None:      # the peers' two ping-pong arenas, as ready-made pointer tables
             stride = self.n_local * self.desc.n_weights * 4
             self._shard_arrays = [_eng.shard_ptr_array([int(q) + c * stride for q in self._peer[1].buffer_ptrs])
                                   for c in (0, 1)]
+        if self._lists is not None and self._lists_valid is not None and self._lists_valid[0] == self.time:
+            # chained: one launch; it also pushes generation time+1's attacks onto the owners' lists
+            if not isinstance(sp, _eng.SoupParams):
+                sp = _eng.make_soup_params(**sp)
+            tabs = self._list_tables()
+            (hc, nc), (hn, nn) = tabs[self.time & 1], tabs[(self.time + 1) & 1]
+            self.backend.soup_chain_peers(self.desc, sp, self._shard_arrays[self._cur], self.n_local, self.rank,
+                                          self.desc.n_weights, self._next, self.seed, self.time, hc, nc, hn, nn,
+                                          self.action, self.dead, stream=stream, flags=tabs[2], wait_gen=self.time - 1)
+            self._lists_valid = (self.time + 1, self._lists_valid[1])
+            return True
         self.backend.soup_sync_peers(self.desc, sp, self._shard_arrays[self._cur], self.n_local, self.rank,
                                      self.desc.n_weights, self._next, self.seed, self.time, self._scratch, self.action,
                                      self.dead, stream=stream)
+        return False
 
     def _peer_flip(self):
         self._cur ^= 1

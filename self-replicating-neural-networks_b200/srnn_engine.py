@@ -28,7 +28,7 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_exact_run", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_exact_run", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_chain_peers", "srnn_soup_push_lists", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
 UIDS_STATIC_MAX = 1 << 24
 
 
@@ -319,6 +319,27 @@ def soup_sync_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, se
                                     C.c_int32(my_shard), C.c_int64(ld), _ptr(w_out), C.c_int64(w_out.shape[1]),
                                     C.c_uint64(seed), C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead),
                                     _stream() if stream is None else C.c_void_p(stream.cuda_stream)))
+
+
+def soup_push_lists(params, n_shards, shard_len, my_shard, seed, gen, heads, nexts, stream=None):
+    """First generation of a chained sharded run: this rank's particles push their attacks onto the owners' lists
+    (heads / nexts: ctypes arrays of every rank's list pointers, see include/srnn_b200.h)."""
+    _chk(lib().srnn_soup_push_lists(C.byref(params), C.c_int32(n_shards), C.c_int64(shard_len), C.c_int32(my_shard),
+                                    C.c_uint64(seed), C.c_uint64(gen), heads, nexts,
+                                    _stream() if stream is None else C.c_void_p(stream.cuda_stream)))
+
+
+def soup_chain_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur, heads_nxt,
+                     nexts_nxt, action=None, loss=None, dead=None, stream=None, flags=None, wait_gen=0):
+    """One generation of a sharded soup whose attack lists are built by the attackers' ranks: ONE launch, which also
+    pushes generation gen+1's attacks (heads_nxt / nexts_nxt, None to skip).  flags / wait_gen: the fused cross-GPU
+    signal that replaces the per-generation barrier (include/srnn_b200.h)."""
+    arr = shard_ptrs if isinstance(shard_ptrs, C.Array) else shard_ptr_array(shard_ptrs)
+    _chk(lib().srnn_soup_chain_peers(C.byref(desc), C.byref(params), arr, C.c_int32(len(arr)), C.c_int64(shard_len),
+                                     C.c_int32(my_shard), C.c_int64(ld), _ptr(w_out), C.c_int64(w_out.shape[1]),
+                                     C.c_uint64(seed), C.c_uint64(gen), heads_cur, nexts_cur, heads_nxt, nexts_nxt,
+                                     flags, C.c_int64(wait_gen), _ptr(action), _ptr(loss), _ptr(dead),
+                                     _stream() if stream is None else C.c_void_p(stream.cuda_stream)))
 
 
 def bind_host_thread_to_gpu(device_index=None):

@@ -337,6 +337,55 @@ def test_soup_sync_bitwise_and_shard_invariance(eng, key, train, sev, path):
         snap, ref = out, rout
 
 
+@pytest.mark.parametrize("key", BENCH_SHAPES)
+@pytest.mark.parametrize("world", [2, 3])
+def test_soup_chain_peers_on_one_gpu(eng, key, world):
+    """srnn_soup_chain_peers / srnn_soup_push_lists, the sharded generation whose attack lists are built by the
+    attackers' owners: `world` shards emulated on one GPU (separate arenas and list arrays, every pointer a "peer"),
+    4 generations == the single-owner oracle run, bit for bit; the list heads are left clean for the next run."""
+    import torch
+    dg, do = both(eng, key)
+    shard = 1100
+    n = shard * world
+    kw = dict(attacking_rate=0.4, learn_from_rate=0.2, train=0, learn_from_severity=1, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population(key, n, seed=77)
+    ref = w.copy()
+    cur = [torch.from_numpy(w[r * shard:(r + 1) * shard].copy()).cuda() for r in range(world)]
+    nxt = [torch.zeros_like(t) for t in cur]
+    lists = [torch.full((2, shard + n), -1, dtype=torch.int32, device="cuda") for _ in range(world)]
+
+    def tables(par):
+        heads = eng.shard_ptr_array([t[par].data_ptr() for t in lists])
+        nexts = eng.shard_ptr_array([t[par].data_ptr() + 4 * shard for t in lists])
+        return heads, nexts
+    h1, n1 = tables(1)
+    for r in range(world):
+        eng.soup_push_lists(pg, world, shard, r, 23, 1, h1, n1)
+    act = [torch.zeros(shard, dtype=torch.uint8, device="cuda") for _ in range(world)]
+    flag_mem = [torch.zeros(world + 1, dtype=torch.int32, device="cuda") for _ in range(world)]
+    flags = eng.shard_ptr_array([t.data_ptr() for t in flag_mem])
+    for gen in range(1, 5):
+        (hc, nc), (hn, nn) = tables(gen & 1), tables((gen + 1) & 1)
+        for r in range(world):
+            # the fused cross-GPU signal: wait (on the device) for generation gen-1 of every rank, signal gen when done
+            eng.soup_chain_peers(dg, pg, [t.data_ptr() for t in cur], shard, r, cur[0].shape[1], nxt[r], 23, gen, hc, nc,
+                                 hn if gen < 4 else None, nn if gen < 4 else None, action=act[r], flags=flags,
+                                 wait_gen=gen - 1)
+        for t in flag_mem:
+            assert t[:world].tolist() == [gen] * world
+        rout = np.zeros_like(ref)
+        ra, _, natt = oracle.soup_sync(do, po, ref, n, rout, 0, n, 23, gen)
+        assert natt > 0.3 * n
+        got = torch.cat(nxt).cpu().numpy()
+        assert_same_weights(got, rout, "gen %d" % gen)
+        assert np.array_equal(torch.cat(act).cpu().numpy(), ra)
+        cur, nxt, ref = nxt, cur, rout
+    for t in lists:
+        assert int((t[:, :shard] != -1).sum().item()) == 0       # every consumed head was reset
+
+
 @pytest.mark.parametrize("key", SHAPES)
 @pytest.mark.parametrize("n", [1, 255, 256, 257, 1000])
 def test_soup_sync_every_fast_shape_and_ragged_tiles(eng, key, n):

@@ -72,7 +72,7 @@ def test_two_ranks_gloo_equals_one(kind, tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("kind", [0, 1, 2])
-@pytest.mark.parametrize("exchange", ["allgather", "peer"])
+@pytest.mark.parametrize("exchange", ["allgather", "peer", "peer_unchained"])
 def test_two_ranks_nccl_equals_one(kind, exchange, tmp_path):
     """all-gather exchange and the fused peer-memory exchange both equal the single-owner result bit for bit."""
     import torch
