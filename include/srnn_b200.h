@@ -193,6 +193,22 @@ int srnn_soup_chain_peers(const srnn_net_desc *d, const srnn_soup_params *p, con
 int srnn_soup_push_lists(const srnn_soup_params *p, int32_t n_shards, int64_t shard_len, int32_t my_shard, uint64_t seed,
                          uint64_t gen, int32_t *const *heads, int32_t *const *nexts, void *stream);
 
+/* Trajectory logging at population scale (particle.save_state at the end of every particle's turn, code/soup.py:87,
+ * for a chosen subset): writes ONE ROW of the caller's device ring buffer for the n_watch particles whose LOCAL indices
+ * are in `watch`, after generation `gen` has run on arena w (and before the respawned slots get their new uids):
+ *   ring_w float[n_watch][n_weights]   record after the generation (the fresh net where the particle was respawned)
+ *   ring_dying float[n_watch][n_weights]  for particles that died: the record they had when the cull test fired (the
+ *                                      state the reference logs for the old particle), taken from the dying side channel
+ *                                      of `p` (include/srnn_types.h); NaN if not dead or the channel overflowed
+ *   ring_action uint8[n_watch] (SRNN_ACT_*), ring_uid int64[n_watch] (uid the particle ran under), ring_loss double[n_watch]
+ *   ring_counterpart int64[n_watch]    GLOBAL INDEX of the teacher if it learned, else of the attack victim, else -1
+ * p, seed, gen must be those of the generation call (the pairing is re-derived, not stored).  loss may be NULL. */
+int srnn_soup_log_watched(const srnn_net_desc *d, const srnn_soup_params *p, const float *w, int64_t ld, int64_t n_total,
+                          int64_t slot0, const int32_t *watch, int32_t n_watch, uint64_t seed, uint64_t gen,
+                          const uint8_t *action, const double *loss, const int64_t *uid_local, float *ring_w,
+                          float *ring_dying, uint8_t *ring_action, int64_t *ring_uid, int64_t *ring_counterpart,
+                          double *ring_loss, void *stream);
+
 /* n_gens consecutive snapshot-synchronous generations (gen0, gen0+1, ...) of an UNSHARDED soup in one call, so a
  * small soup is not bound by the host's per-call overhead: generation gen0+g reads w_a and writes w_b for even g,
  * the other way round for odd g -- the newest arena is w_b if n_gens is odd, else w_a.  Same arguments and

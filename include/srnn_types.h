@@ -66,6 +66,13 @@ typedef struct srnn_soup_params {
     int32_t perm_mode;           /* SRNN_PERM_NONE or SRNN_PERM_PHILOX            */
     int32_t engine_path;         /* srnn_soup_sync*: 0 auto, 1 fused kernel per generation, 2 multi-pass, 3 persistent
                                     cooperative kernel for srnn_soup_sync_run (all give the same results) */
+    /* trajectory side channel (optional; all zero = off): the generation kernels append every particle that dies -- its
+     * GLOBAL index and the record it had when the cull test fired, i.e. what particle.save_state would have logged for
+     * the old particle (code/soup.py:77-87) -- before the slot is respawned.  Used by srnn_soup_log_watched. */
+    int32_t dying_cap;           /* capacity of the two arrays below, in records                                  */
+    float   *dying_w;            /* device float[dying_cap][n_weights]                                            */
+    int64_t *dying_idx;          /* device int64[dying_cap]                                                       */
+    int32_t *dying_count;        /* device int32, zeroed by the caller; may end above dying_cap (excess dropped)   */
 } srnn_soup_params;
 
 #define SRNN_MAX_WEIGHTS 64      /* per-net weight count supported by the generic code paths */

@@ -31,7 +31,8 @@ class SoupParams(C.Structure):
     _fields_ = [("attacking_rate", C.c_double), ("learn_from_rate", C.c_double), ("train", C.c_int32),
                 ("learn_from_severity", C.c_int32), ("remove_divergent", C.c_int32), ("remove_zero", C.c_int32),
                 ("epsilon", C.c_double), ("lr", C.c_float), ("perm_mode", C.c_int32),
-                ("engine_path", C.c_int32)]
+                ("engine_path", C.c_int32), ("dying_cap", C.c_int32), ("dying_w", C.c_void_p),
+                ("dying_idx", C.c_void_p), ("dying_count", C.c_void_p)]
 
 
 def build(force=False):
@@ -74,7 +75,7 @@ def rnn(width=2, depth=2):
 def soup_params(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, remove_divergent=False,
                 remove_zero=False, epsilon=1e-14, lr=0.01, perm_mode=PERM_NONE, engine_path=0):
     return SoupParams(attacking_rate, learn_from_rate, train, learn_from_severity, int(bool(remove_divergent)),
-                      int(bool(remove_zero)), epsilon, lr, perm_mode, engine_path)
+                      int(bool(remove_zero)), epsilon, lr, perm_mode, engine_path, 0, None, None, None)
 
 
 def _f32(a):

@@ -673,7 +673,22 @@ struct SoupP {
     float lr;
     Eps eps;
     int path;  // 0 auto, 1 fused single kernel, 2 multi-pass
+    int dying_cap;          // trajectory side channel (include/srnn_types.h): pre-respawn records of the particles that die
+    float *dying_w;
+    int64_t *dying_idx;
+    int *dying_count;
 };
+// a particle is about to be respawned: keep what save_state would have logged for it (code/soup.py:77-87)
+template <int NW>
+__device__ __forceinline__ void log_dying(const SoupP &p, int64_t global_index, const float *rec) {
+    if (!p.dying_count) return;
+    const int pos = atomicAdd(p.dying_count, 1);
+    if (pos < p.dying_cap) {
+        p.dying_idx[pos] = global_index;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) p.dying_w[(int64_t)pos * NW + k] = rec[k];
+    }
+}
 
 __device__ __forceinline__ void soup_draw(const SoupP &p, uint64_t seed, uint64_t slot, uint64_t gen,
                                           int64_t n_total, int64_t *att, int64_t *lrn) {
@@ -717,6 +732,7 @@ __device__ __forceinline__ void soup_tail(const SoupP &p, float *cur, const SgdS
     if (p.remove_divergent && is_diverged<S::NW>(cur)) { d = true; *action = SRNN_ACT_DIV_DEAD; }
     if (p.remove_zero && is_zero<S::NW>(cur, p.eps.le)) { d = true; *action = SRNN_ACT_ZERO_DEAD; }
     if (d) {  // respawn: next caller-supplied spare record (generator() output) if one is left, else Philox init
+        log_dying<S::NW>(p, (int64_t)slot, cur);
         if (spares && spares_used && *spares_used < n_spares) {
             const float *sp = spares + (int64_t)(*spares_used) * spare_ld;
 #pragma unroll
@@ -1248,6 +1264,10 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     for (int q = tid; q < q_len; q += SBS) {
         const int v = queue[q];
         float fresh[NW];
+        if (p.dying_count) {
+            tile_get<NW>(tile, v, fresh);
+            log_dying<NW>(p, slot0 + base + v, fresh);
+        }
         init_net<S>(seed, (uint64_t)(slot0 + base + v), (uint32_t)gen, lim, fresh);
         tile_put<NW>(tile, v, fresh);
     }
@@ -1634,6 +1654,10 @@ __global__ void __launch_bounds__(BS) soup_final_kernel(const float *__restrict_
     if (tid < q_len) {  // respawn, compacted within the CTA
         const int v = queue[tid];
         float fresh[NW];
+        if (p.dying_count) {
+            tile_get<NW>(tile, v, fresh);
+            log_dying<NW>(p, slot0 + base + v, fresh);
+        }
         init_net<S>(seed, (uint64_t)(slot0 + base + v), (uint32_t)gen, lim, fresh);
         tile_put<NW>(tile, v, fresh);
     }
@@ -1750,6 +1774,10 @@ static int make_soup(const srnn_soup_params *p, SoupP *q) {
     q->perm_mode = p->perm_mode;
     q->lr = p->lr;
     q->path = p->engine_path;
+    q->dying_cap = p->dying_count ? p->dying_cap : 0;
+    q->dying_w = p->dying_w;
+    q->dying_idx = p->dying_idx;
+    q->dying_count = (p->dying_count && p->dying_w && p->dying_idx && p->dying_cap > 0) ? p->dying_count : nullptr;
     if (p->perm_mode != SRNN_PERM_NONE && p->perm_mode != SRNN_PERM_PHILOX)
         return fail(SRNN_ERR_ARG, "soup perm_mode must be SRNN_PERM_NONE or SRNN_PERM_PHILOX%s");
     return make_eps(p->epsilon, &q->eps);
@@ -2131,6 +2159,60 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
     tab.n = n_shards;
     return soup_sync_impl(d, p, tab, shards[my_shard], ld, shard_len * n_shards, w_out, out_ld, (int64_t)my_shard * shard_len,
                           shard_len, seed, gen, scratch, action, loss, dead, stream);
+}
+
+// ---- trajectory ring: one row of the caller's ring buffer per logged generation.  One thread per watched
+// particle gathers what particle.save_state(**description) records at code/soup.py:55-87 -- the record after the
+// generation, the action that won the precedence, the loss of the last train epoch, the uid it ran under, the global
+// index of its counterpart (attack victim / teacher, re-derived from the pairing function) -- and, when it died, the
+// record it had before the respawn (looked up in the dying side channel; NaN when that overflowed).
+__global__ void soup_log_watched_kernel(const float *__restrict__ w, int64_t ld, int nw, int64_t n_total, int64_t slot0,
+                                        const int32_t *__restrict__ watch, int n_watch, SoupP p, uint64_t seed, uint64_t gen,
+                                        const uint8_t *__restrict__ action, const double *__restrict__ loss,
+                                        const int64_t *__restrict__ uid_local, float *ring_w, float *ring_dying,
+                                        uint8_t *ring_action, int64_t *ring_uid, int64_t *ring_counterpart,
+                                        double *ring_loss) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_watch) return;
+    const int64_t v = watch[i];
+    const uint8_t act = action[v];
+    for (int k = 0; k < nw; ++k) ring_w[(int64_t)i * nw + k] = w[v * ld + k];
+    ring_action[i] = act;
+    ring_uid[i] = uid_local[v];
+    ring_loss[i] = loss ? loss[v] : nan("");
+    int64_t at, lr;
+    soup_draw(p, seed, (uint64_t)(slot0 + v), gen, n_total, &at, &lr);
+    // code/soup.py:56-68: the learn_from description overwrites the attack's; train_self sets counterpart None
+    ring_counterpart[i] = lr >= 0 ? lr : at;
+    const bool died = act == SRNN_ACT_DIV_DEAD || act == SRNN_ACT_ZERO_DEAD;
+    int found = -1;
+    if (died && p.dying_count) {
+        const int cnt = min(*p.dying_count, p.dying_cap);
+        for (int q = 0; q < cnt; ++q)
+            if (p.dying_idx[q] == slot0 + v) { found = q; break; }
+    }
+    for (int k = 0; k < nw; ++k)
+        ring_dying[(int64_t)i * nw + k] = found >= 0 ? p.dying_w[(int64_t)found * nw + k] : nanf("");
+}
+
+int srnn_soup_log_watched(const srnn_net_desc *d, const srnn_soup_params *p, const float *w, int64_t ld, int64_t n_total,
+                          int64_t slot0, const int32_t *watch, int32_t n_watch, uint64_t seed, uint64_t gen,
+                          const uint8_t *action, const double *loss, const int64_t *uid_local, float *ring_w,
+                          float *ring_dying, uint8_t *ring_action, int64_t *ring_uid, int64_t *ring_counterpart,
+                          double *ring_loss, void *stream) {
+    if (!d || !w || !watch || !action || !uid_local || !ring_w || !ring_dying || !ring_action || !ring_uid ||
+        !ring_counterpart || !ring_loss)
+        return fail(SRNN_ERR_ARG, "srnn_soup_log_watched: a required pointer is NULL%s");
+    if (n_watch <= 0) return n_watch == 0 ? SRNN_OK : fail(SRNN_ERR_ARG, "n_watch < 0%s");
+    srnn_net_desc dd = *d;
+    if (srnn_desc_init(&dd) != SRNN_OK || ld < dd.n_weights) return fail(SRNN_ERR_ARG, "bad descriptor or record stride%s");
+    SoupP q;
+    int rc = make_soup(p, &q);
+    if (rc) return rc;
+    soup_log_watched_kernel<<<(n_watch + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+        w, ld, dd.n_weights, n_total, slot0, watch, n_watch, q, seed, gen, action, loss, uid_local, ring_w, ring_dying,
+        ring_action, ring_uid, ring_counterpart, ring_loss);
+    return check_launch("srnn_soup_log_watched");
 }
 
 static int fill_list_table(PeerListTable *t, int32_t *const *heads, int32_t *const *nexts, int32_t n_shards) {

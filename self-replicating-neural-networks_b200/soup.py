@@ -232,15 +232,15 @@ class _CudaBackend:
     def init(self, desc, w, seed, slot0, generation):
         _eng.Population(desc, w.shape[0], device=self.device, ld=w.shape[1], w=w).init(seed, slot0=slot0, generation=generation)
 
-    def soup_sync(self, desc, sp_kwargs, snap, n_total, w_out, slot0, n, seed, gen, scratch, action, dead):
+    def soup_sync(self, desc, sp_kwargs, snap, n_total, w_out, slot0, n, seed, gen, scratch, action, dead, loss=None):
         _eng.soup_sync(desc, _eng.make_soup_params(**sp_kwargs), snap, n_total, w_out, slot0, n, seed, gen, scratch,
-                       action=action, dead=dead)
+                       action=action, dead=dead, loss=loss)
 
     def soup_sync_peers(self, desc, sp_kwargs, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action,
-                        dead, stream=None):
+                        dead, stream=None, loss=None):
         sp = sp_kwargs if isinstance(sp_kwargs, _eng.SoupParams) else _eng.make_soup_params(**sp_kwargs)
         _eng.soup_sync_peers(desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, scratch, action=action,
-                             dead=dead, stream=stream)
+                             dead=dead, stream=stream, loss=loss)
 
     def peer_arena(self, n_local, nw, group):
         """Two ping-pong arenas in NVLink-mapped symmetric memory: returns (tensor (2, n_local, nw), handle) or None
@@ -280,13 +280,20 @@ class _CudaBackend:
         _eng.soup_push_lists(sp, n_shards, shard_len, my_shard, seed, gen, heads, nexts, stream=stream)
 
     def soup_chain_peers(self, desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur,
-                         heads_nxt, nexts_nxt, action, dead, stream=None, flags=None, wait_gen=0):
+                         heads_nxt, nexts_nxt, action, dead, stream=None, flags=None, wait_gen=0, loss=None):
         _eng.soup_chain_peers(desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur,
-                              heads_nxt, nexts_nxt, action=action, dead=dead, stream=stream, flags=flags, wait_gen=wait_gen)
+                              heads_nxt, nexts_nxt, action=action, dead=dead, stream=stream, flags=flags, wait_gen=wait_gen,
+                              loss=loss)
 
-    def soup_exact(self, desc, sp_kwargs, w, seed, gen0, n_gens, scratch, action, dead, rounds):
-        _eng.soup_exact_run(desc, _eng.make_soup_params(**sp_kwargs), w, seed, gen0, n_gens, scratch, action=action,
-                            dead=dead, rounds=rounds)
+    def soup_exact(self, desc, sp_kwargs, w, seed, gen0, n_gens, scratch, action, dead, rounds, loss=None):
+        sp = _eng.make_soup_params(**sp_kwargs)
+        if loss is not None and n_gens == 1:       # the single-generation entry also returns the losses
+            _eng.soup_exact(desc, sp, w, seed, gen0, scratch, action=action, loss=loss, dead=dead, want_rounds=False)
+            return
+        _eng.soup_exact_run(desc, sp, w, seed, gen0, n_gens, scratch, action=action, dead=dead, rounds=rounds)
+
+    def soup_log_watched(self, desc, sp_kwargs, *args):
+        _eng.soup_log_watched(desc, _eng.make_soup_params(**sp_kwargs), *args)
 
     def soup_sync_run(self, desc, sp_kwargs, w_a, w_b, seed, gen0, n_gens, scratch, action, dead):
         _eng.soup_sync_run(desc, _eng.make_soup_params(**sp_kwargs), w_a, w_b, seed, gen0, n_gens, scratch,
@@ -465,8 +472,11 @@ class PopulationSoup:
         return self
 
     def _sp(self):
-        return {k: self.params[k] for k in ("attacking_rate", "learn_from_rate", "train", "learn_from_severity",
-                                            "remove_divergent", "remove_zero", "epsilon", "perm_mode", "engine_path")}
+        sp = {k: self.params[k] for k in ("attacking_rate", "learn_from_rate", "train", "learn_from_severity",
+                                          "remove_divergent", "remove_zero", "epsilon", "perm_mode", "engine_path")}
+        if self._watch is not None:
+            sp["dying"] = self._watch["dying"]      # pre-respawn records of the particles that die (trajectory log)
+        return sp
 
     def evolve(self, iterations=1):
         import torch.distributed as dist
@@ -480,8 +490,9 @@ class PopulationSoup:
             while done < iterations:
                 k = min(step, iterations - done)
                 self._rounds = B.alloc((k,), torch.int32) if hasattr(B, "alloc") else None
+                self._pre_generation()
                 B.soup_exact(self.desc, sp, self.w, self.seed, self.time + 1, k, self._scratch, self.action, self.dead,
-                             self._rounds)
+                             self._rounds, **self._loss_kw())
                 self.time += k
                 done += k
                 if self.track_uids:
@@ -515,8 +526,9 @@ class PopulationSoup:
                 snap = self._snap
             else:
                 snap = self.w
+            self._pre_generation()
             B.soup_sync(self.desc, sp, snap, self.size, self._next, self.slot0, self.n_local, self.seed, self.time,
-                        self._scratch, self.action, self.dead)
+                        self._scratch, self.action, self.dead, **self._loss_kw())
             self.w, self._next = self._next, self.w
             if self.track_uids:
                 self._assign_uids()
@@ -536,7 +548,7 @@ class PopulationSoup:
         return self._list_ptrs
 
     def _params_key(self):
-        return tuple(sorted((k, float(v) if isinstance(v, float) else v) for k, v in self._sp().items()))
+        return tuple(sorted((k, float(v) if isinstance(v, float) else v) for k, v in self._sp().items() if k != "dying"))
 
     def _chain_stale(self):
         """True when the lists of generation time+1 still have to be built (first run, parameters changed, or the soup
@@ -577,14 +589,17 @@ class PopulationSoup:
                 sp = _eng.make_soup_params(**sp)
             tabs = self._list_tables()
             (hc, nc), (hn, nn) = tabs[self.time & 1], tabs[(self.time + 1) & 1]
+            self._pre_generation()
             self.backend.soup_chain_peers(self.desc, sp, self._shard_arrays[self._cur], self.n_local, self.rank,
                                           self.desc.n_weights, self._next, self.seed, self.time, hc, nc, hn, nn,
-                                          self.action, self.dead, stream=stream, flags=tabs[2], wait_gen=self.time - 1)
+                                          self.action, self.dead, stream=stream, flags=tabs[2], wait_gen=self.time - 1,
+                                          **self._loss_kw())
             self._lists_valid = (self.time + 1, self._lists_valid[1])
             return True
+        self._pre_generation()
         self.backend.soup_sync_peers(self.desc, sp, self._shard_arrays[self._cur], self.n_local, self.rank,
                                      self.desc.n_weights, self._next, self.seed, self.time, self._scratch, self.action,
-                                     self.dead, stream=stream)
+                                     self.dead, stream=stream, **self._loss_kw())
         return False
 
     def _peer_flip(self):
@@ -598,6 +613,9 @@ class PopulationSoup:
         """Deterministic global uids for respawned particles: rank offsets from an all-gather of per-rank counts."""
         import torch
         import torch.distributed as dist
+        logging = self._logging_now()
+        if logging:
+            self._log_before_uids()
         mine = self.dead.sum(dtype=torch.int64).reshape(1)
         if self.world > 1:
             counts = torch.zeros(self.world, dtype=torch.int64, device=mine.device)
@@ -607,40 +625,133 @@ class PopulationSoup:
             counts = [int(mine.item())]
         base, self.next_uid = uid_base_of(self.rank, counts, self.next_uid)
         self.backend.assign_uids(self.dead, self.uid, base, self._uid_tmp, self._n_dead)
+        if logging:
+            self._log_after_uids()
 
     # ---- trajectory logging at scale: the reference logs every particle every generation
-    #      (code/soup.py:87); a 10 M-particle soup logs a chosen subset, every k-th generation, in the same schema
-    def watch(self, particles, every=1):
+    #      (code/soup.py:87); a 10 M-particle soup logs a chosen subset, every k-th generation, in the same schema.
+    #      The states are gathered ON THE DEVICE into a ring buffer (srnn_soup_log_watched: weights, action, counterpart,
+    #      loss, the record a dying particle had before its respawn) and come to the host once per `capacity` logged
+    #      generations -- not with a .cpu() per generation.
+    def watch(self, particles, every=1, capacity=64):
         """Record the states of the given GLOBAL particle indices (those owned by this rank) every `every` generations.
         Turns on uid tracking so respawned particles start a new trajectory under a new uid, as in the reference."""
         import torch
         mine = [int(g) - self.slot0 for g in particles if self.slot0 <= int(g) < self.slot0 + self.n_local]
-        self._watch = (torch.as_tensor(mine, dtype=torch.int64, device=self.w.device), int(every), {})
+        B, nw, W, K = self.backend, self.desc.n_weights, len(mine), int(capacity)
+        idx = B.alloc((max(W, 1),), torch.int32)
+        idx[:W] = torch.as_tensor(mine, dtype=torch.int32)
+        cap = max(1024, self.n_local // 64)
+        self._watch = dict(
+            idx=idx[:W], every=int(every), K=K, rows=0, times=[], log={},
+            ring_w=B.alloc((K, max(W, 1), nw), torch.float32), ring_dying=B.alloc((K, max(W, 1), nw), torch.float32),
+            ring_action=B.alloc((K, max(W, 1)), torch.uint8), ring_uid=B.alloc((K, max(W, 1)), torch.int64),
+            ring_cp=B.alloc((K, max(W, 1)), torch.int64), ring_cpuid=B.alloc((K, max(W, 1)), torch.int64),
+            ring_newuid=B.alloc((K, max(W, 1)), torch.int64), ring_loss=B.alloc((K, max(W, 1)), torch.float64),
+            dying=(B.alloc((cap, nw), torch.float32), B.alloc((cap,), torch.int64), B.alloc((1,), torch.int32)),
+            loss=B.alloc((self.n_local,), torch.float64))
         self.track_uids = True
-        self._log_watched(first=True)
+        if W:                                   # ParticleDecorator.__init__ logs the 'init' state at time 0
+            w0 = self.w[self._watch["idx"].long(), :nw].cpu().numpy()
+            u0 = self.uid[self._watch["idx"].long()].cpu().numpy()
+            name = _eng.KIND_NAMES[self.desc.kind]
+            for row in range(W):
+                if np.isfinite(w0[row]).all():
+                    self._watch["log"].setdefault(int(u0[row]), []).append(
+                        {'class': name, 'weights': w0[row].copy(), 'time': 0, 'action': 'init', 'counterpart': None})
         return self
 
-    def _log_watched(self, first=False):
-        if self._watch is None or (not first and self.time % self._watch[1]):
+    def _logging_now(self):
+        return self._watch is not None and self._watch["idx"].numel() > 0 and self.time % self._watch["every"] == 0
+
+    def _pre_generation(self):
+        """Called right before generation self.time is launched."""
+        if self._watch is not None:
+            self._watch["dying"][2].zero_()
+
+    def _loss_kw(self):
+        return {} if self._watch is None else {"loss": self._watch["loss"]}
+
+    def _log_before_uids(self):
+        """After generation self.time, before the respawned slots get their new uids: one ring row, on the device."""
+        import torch
+        import torch.distributed as dist
+        wt = self._watch
+        r = wt["rows"]
+        self.backend.soup_log_watched(self.desc, self._sp(), self.w, self.size, self.slot0, wt["idx"], self.seed, self.time,
+                                      self.action, wt["loss"], self.uid, wt["ring_w"][r], wt["ring_dying"][r],
+                                      wt["ring_action"][r], wt["ring_uid"][r], wt["ring_cp"][r], wt["ring_loss"][r])
+        # counterpart: global index -> the uid that particle had when the generation started (other_particle.get_uid())
+        uid_all = self.uid
+        if self.world > 1:
+            uid_all = torch.zeros(self.size, dtype=torch.int64, device=self.uid.device)
+            dist.all_gather_into_tensor(uid_all, self.uid, group=self.group)
+        W = wt["idx"].numel()
+        cp = wt["ring_cp"][r, :W]
+        wt["ring_cpuid"][r, :W] = torch.where(cp >= 0, uid_all[cp.clamp(min=0)], cp)
+
+    def _log_after_uids(self):
+        wt = self._watch
+        r, W = wt["rows"], wt["idx"].numel()
+        wt["ring_newuid"][r, :W] = self.uid[wt["idx"].long()]
+        wt["times"].append(self.time)
+        wt["rows"] = r + 1
+        if wt["rows"] == wt["K"]:
+            self._drain_watch()
+
+    def _log_watched(self):
+        """Kept for the generation loops: the ring row of a generation is written around the uid assignment, see
+        _assign_uids; nothing to do here."""
+        return
+
+    def _drain_watch(self):
+        """Ring -> host: ONE copy per buffer, then the reference's state dicts (code/network.py:185-198, soup.py:55-87)."""
+        wt = self._watch
+        if wt is None or wt["rows"] == 0:
             return
-        idx, _, log = self._watch
-        if idx.numel() == 0:
-            return
-        w = self.w[idx, :self.desc.n_weights].cpu().numpy()
-        uid = self.uid[idx].cpu().numpy()
-        act = self.action[idx].cpu().numpy()
+        r, W = wt["rows"], wt["idx"].numel()
         name = _eng.KIND_NAMES[self.desc.kind]
-        for row in range(idx.numel()):
-            if not np.isfinite(w[row]).all():          # ParticleDecorator.make_state drops non-finite states
-                continue
-            state = {'class': name, 'weights': w[row].copy(), 'time': self.time,
-                     'action': 'init' if first else _eng.ACT_NAMES[int(act[row])], 'counterpart': None}
-            log.setdefault(int(uid[row]), []).append(state)
+        w = wt["ring_w"][:r, :W].cpu().numpy()
+        dying = wt["ring_dying"][:r, :W].cpu().numpy()
+        act = wt["ring_action"][:r, :W].cpu().numpy()
+        uid = wt["ring_uid"][:r, :W].cpu().numpy()
+        cpuid = wt["ring_cpuid"][:r, :W].cpu().numpy()
+        newuid = wt["ring_newuid"][:r, :W].cpu().numpy()
+        loss = wt["ring_loss"][:r, :W].cpu().numpy()
+        train = int(self.params.get("train", 0) or 0)
+        log = wt["log"]
+        for row, t in enumerate(wt["times"]):
+            for j in range(W):
+                a = int(act[row, j])
+                state = {'class': name, 'time': t}
+                if a in (4, 5):                # the old particle's last state, then a new trajectory under the new uid
+                    if train > 0:
+                        state.update(fitted=train, loss=float(loss[row, j]))
+                    state.update(action=_eng.ACT_NAMES[a], counterpart=int(newuid[row, j]))
+                    if np.isfinite(dying[row, j]).all():       # make_state drops non-finite states (network.py:187-188)
+                        state['weights'] = dying[row, j].copy()
+                        log.setdefault(int(uid[row, j]), []).append(state)
+                    if np.isfinite(w[row, j]).all():
+                        log.setdefault(int(newuid[row, j]), []).append(
+                            {'class': name, 'weights': w[row, j].copy(), 'time': 0, 'action': 'init', 'counterpart': None})
+                    continue
+                if not np.isfinite(w[row, j]).all():
+                    continue
+                state['weights'] = w[row, j].copy()
+                if a in (1, 2):
+                    state.update(action=_eng.ACT_NAMES[a], counterpart=int(cpuid[row, j]))
+                elif a == 3:
+                    state.update(fitted=train, loss=float(loss[row, j]), action='train_self', counterpart=None)
+                log.setdefault(int(uid[row, j]), []).append(state)
+        wt["rows"], wt["times"] = 0, []
 
     def historical_particles(self):
         """uid -> list of state dicts for the watched particles: the structure Soup.without_particles() pickles and the
-        reference's visualization.py reads (code/visualization.py:27-40)."""
-        return {} if self._watch is None else self._watch[2]
+        reference's visualization.py reads (code/visualization.py:27-40).  Drains the device ring first."""
+        if self._watch is None:
+            return {}
+        self._drain_watch()
+        return self._watch["log"]
 
     # ---- checkpoint / resume (the reference can only dill-dump finished experiments, code/experiment.py:56-59)
     def state_dict(self):

@@ -28,7 +28,7 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_exact_run", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_chain_peers", "srnn_soup_push_lists", "srnn_soup_sync_run", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_exact_run", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_chain_peers", "srnn_soup_push_lists", "srnn_soup_sync_run", "srnn_soup_log_watched", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
 UIDS_STATIC_MAX = 1 << 24
 
 
@@ -44,7 +44,8 @@ class SoupParams(C.Structure):
     _fields_ = [("attacking_rate", C.c_double), ("learn_from_rate", C.c_double), ("train", C.c_int32),
                 ("learn_from_severity", C.c_int32), ("remove_divergent", C.c_int32), ("remove_zero", C.c_int32),
                 ("epsilon", C.c_double), ("lr", C.c_float), ("perm_mode", C.c_int32),
-                ("engine_path", C.c_int32)]
+                ("engine_path", C.c_int32), ("dying_cap", C.c_int32), ("dying_w", C.c_void_p),
+                ("dying_idx", C.c_void_p), ("dying_count", C.c_void_p)]
 
 
 class SrnnError(RuntimeError):
@@ -98,10 +99,16 @@ def layer_shapes(d):
 
 
 def make_soup_params(attacking_rate=0.1, learn_from_rate=0.1, train=0, learn_from_severity=1, remove_divergent=False,
-                     remove_zero=False, epsilon=1e-14, lr=0.01, perm_mode=PERM_NONE, engine_path=0):
-    return SoupParams(float(attacking_rate), float(learn_from_rate), int(train), int(learn_from_severity),
-                      int(bool(remove_divergent)), int(bool(remove_zero)), float(epsilon), float(lr), int(perm_mode),
-                      int(engine_path))
+                     remove_zero=False, epsilon=1e-14, lr=0.01, perm_mode=PERM_NONE, engine_path=0, dying=None):
+    """dying: optional (records float tensor [cap][n_weights], indices int64 tensor [cap], count int32 tensor [1]) --
+    the side channel that keeps the pre-respawn record of every particle that dies (trajectory logging)."""
+    sp = SoupParams(float(attacking_rate), float(learn_from_rate), int(train), int(learn_from_severity),
+                    int(bool(remove_divergent)), int(bool(remove_zero)), float(epsilon), float(lr), int(perm_mode),
+                    int(engine_path), 0, None, None, None)
+    if dying is not None:
+        rec, idx, cnt = dying
+        sp.dying_cap, sp.dying_w, sp.dying_idx, sp.dying_count = int(idx.numel()), rec.data_ptr(), idx.data_ptr(), cnt.data_ptr()
+    return sp
 
 
 def soup_scratch_len(n_total, n):
@@ -286,13 +293,15 @@ def soup_sync(desc, params, snap, n_total, w_out, slot0, n, seed, gen, scratch, 
                               C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead), _stream()))
 
 
-def soup_exact(desc, params, w, seed, gen, scratch, att=None, lrn=None, action=None, loss=None, dead=None):
+def soup_exact(desc, params, w, seed, gen, scratch, att=None, lrn=None, action=None, loss=None, dead=None,
+               want_rounds=True):
     """One generation with the reference's exact sequential semantics, run as a parallel wavefront (in place on w).
-    att / lrn: int64 device tensors of targets (or None for Philox draws).  Returns the number of rounds."""
+    att / lrn: int64 device tensors of targets (or None for Philox draws).  Returns the dependency depth (this waits
+    for the stream) unless want_rounds is False (fully asynchronous)."""
     rounds = C.c_int32(0)
     _chk(lib().srnn_soup_exact(C.byref(desc), C.byref(params), _ptr(w), C.c_int64(w.shape[1]), C.c_int64(w.shape[0]),
                                _ptr(att), _ptr(lrn), C.c_uint64(seed), C.c_uint64(gen), _ptr(scratch), _ptr(action),
-                               _ptr(loss), _ptr(dead), C.byref(rounds), _stream()))
+                               _ptr(loss), _ptr(dead), C.byref(rounds) if want_rounds else None, _stream()))
     return rounds.value
 
 
@@ -319,6 +328,16 @@ def soup_sync_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, se
                                     C.c_int32(my_shard), C.c_int64(ld), _ptr(w_out), C.c_int64(w_out.shape[1]),
                                     C.c_uint64(seed), C.c_uint64(gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead),
                                     _stream() if stream is None else C.c_void_p(stream.cuda_stream)))
+
+
+def soup_log_watched(desc, params, w, n_total, slot0, watch, seed, gen, action, loss, uid_local, ring_w, ring_dying,
+                     ring_action, ring_uid, ring_counterpart, ring_loss):
+    """One row of the trajectory ring for the watched local indices (include/srnn_b200.h: srnn_soup_log_watched)."""
+    _chk(lib().srnn_soup_log_watched(C.byref(desc), C.byref(params), _ptr(w), C.c_int64(w.shape[1]), C.c_int64(n_total),
+                                     C.c_int64(slot0), _ptr(watch), C.c_int32(watch.numel()), C.c_uint64(seed),
+                                     C.c_uint64(gen), _ptr(action), _ptr(loss), _ptr(uid_local), _ptr(ring_w),
+                                     _ptr(ring_dying), _ptr(ring_action), _ptr(ring_uid), _ptr(ring_counterpart),
+                                     _ptr(ring_loss), _stream()))
 
 
 def soup_push_lists(params, n_shards, shard_len, my_shard, seed, gen, heads, nexts, stream=None):

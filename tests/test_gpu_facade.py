@@ -385,29 +385,86 @@ def test_multi_generation_runs_equal_per_generation_launches(api, kind, n, gens,
 
 
 def test_population_soup_watch_trajectories(api, tmp_path, monkeypatch):
-    """Trajectory logging at scale: watched particles of a PopulationSoup produce the reference's state-dict schema
-    (uid -> [{class, weights, time, action, counterpart}]), respawns start a new uid, and the result pickles through
-    Experiment.save like the reference's soups."""
+    """Trajectory logging at scale (device ring buffer, srnn_soup_log_watched): watched particles of a PopulationSoup
+    produce the reference's state dicts (code/soup.py:55-87, code/network.py:185-198) -- checked against the oracle's
+    run of the same soup: weights per logged generation, the action that won the precedence, the counterpart's uid, the
+    dying particle's last state under its OLD uid, a fresh trajectory starting with 'init' at time 0 under the new uid --
+    and the result pickles through Experiment.save like the reference's soups."""
     network, soup_mod, experiment = api
+    import oracle
     import srnn_engine as eng
     monkeypatch.chdir(tmp_path)
-    n = 2000
-    s = soup_mod.PopulationSoup(eng.KIND_WW, n, seed=5, attacking_rate=0.5, learn_from_rate=0.1, train=0,
-                                remove_divergent=True, remove_zero=True).seed_particles()
-    s.watch(range(0, n, 100), every=2)
-    s.evolve(10)
+    n, gens = 2000, 10
+    kw = dict(attacking_rate=0.5, learn_from_rate=0.1, train=0, learn_from_severity=1, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4)
+    s = soup_mod.PopulationSoup(eng.KIND_WW, n, seed=5, **kw).seed_particles()
+    watched = list(range(0, n, 100))
+    w0 = s.local.numpy().copy()
+    s.watch(watched, every=2, capacity=3)                 # capacity 3: the ring is drained twice on the way
+    s.evolve(gens)
     hp = s.historical_particles()
-    assert len(hp) >= 20                                  # 20 watched slots, plus new uids for respawned ones
-    assert any(uid >= n for uid in hp)                    # with attack 0.5 and no training, some watched particle died
-    for uid, states in hp.items():
-        times = [st['time'] for st in states]
-        assert times == sorted(times) and all(t % 2 == 0 for t in times)
-        for st in states:
-            assert set(st) == {'class', 'weights', 'time', 'action', 'counterpart'}
-            assert st['class'] == 'WeightwiseNeuralNetwork' and st['weights'].shape == (14,)
-            assert st['action'] in ('init', None, 'attacking', 'learn_from', 'train_self', 'divergent_dead', 'zweo_dead')
+    # ---- the same soup on the oracle, keeping what the reference would log
+    do, po = oracle.ww(), oracle.soup_params(perm_mode=2, **kw)
+    w, uid, next_uid = w0.copy(), np.arange(n), n
+    want = {u: [dict(time=0, action='init', counterpart=None, weights=w0[u].copy())] for u in watched}
+    for g in range(1, gens + 1):
+        out = np.zeros_like(w)
+        act, _, _ = oracle.soup_sync(do, po, w, n, out, 0, n, 5, g)
+        att, lrn = oracle.soup_draw(po, 5, g, n)
+        dead = act >= 4
+        new_uid = uid.copy()
+        new_uid[dead] = next_uid + np.arange(int(dead.sum()))
+        next_uid += int(dead.sum())
+        if g % 2 == 0:
+            for v in watched:
+                a = int(act[v])
+                if a >= 4:
+                    want.setdefault(int(uid[v]), []).append(dict(time=g, action=eng.ACT_NAMES[a], counterpart=int(new_uid[v])))
+                    want.setdefault(int(new_uid[v]), []).append(dict(time=0, action='init', counterpart=None, weights=out[v].copy()))
+                elif np.isfinite(out[v]).all():
+                    st = dict(time=g, weights=out[v].copy())
+                    if a in (1, 2):
+                        st.update(action=eng.ACT_NAMES[a], counterpart=int(uid[lrn[v]] if lrn[v] >= 0 else uid[att[v]]))
+                    want.setdefault(int(uid[v]), []).append(st)
+        w, uid = out, new_uid
+    assert any(u >= n for u in hp)                        # with attack 0.5 and no training some watched particle died
+    for u, states in want.items():
+        got = hp.get(u, [])
+        # a dying state is only logged when the pre-respawn record is finite (ParticleDecorator.make_state)
+        exp_states = [st for st in states if 'weights' in st or st['action'] not in ('divergent_dead', 'zweo_dead')]
+        dying = [st for st in states if st.get('action') in ('divergent_dead', 'zweo_dead')]
+        got_core = [st for st in got if st.get('action') not in ('divergent_dead', 'zweo_dead')]
+        assert len(got_core) == len(exp_states), (u, got, states)
+        for gs, es in zip(got_core, exp_states):
+            assert gs['class'] == 'WeightwiseNeuralNetwork' and gs['time'] == es['time']
+            assert gs.get('action') == es.get('action') and gs.get('counterpart') == es.get('counterpart')
+            assert np.array_equal(gs['weights'].view(np.uint32), es['weights'].view(np.uint32))
+        for gs in got:
+            if gs.get('action') in ('divergent_dead', 'zweo_dead'):
+                assert len(dying) == 1 and gs['time'] == dying[0]['time'] and gs['counterpart'] == dying[0]['counterpart']
+                assert np.isfinite(gs['weights']).all()
+                if gs['action'] == 'zweo_dead':
+                    assert np.abs(gs['weights']).max() <= 1e-4
+    assert set(hp) <= set(want)
     with experiment.SoupExperiment("population-soup") as exp:
         exp.save(soup_states=hp)
     back = experiment.Experiment.from_dill(os.path.join(exp.dir, "soup_states.dill"))
     assert set(back) == set(hp)
 
+
+def test_population_soup_watch_train_loss(api):
+    """With train > 0 the logged states carry the reference's extra keys: fitted = train, loss = the last epoch's."""
+    network, soup_mod, experiment = api
+    import srnn_engine as eng
+    s = soup_mod.PopulationSoup(eng.KIND_WW, 512, seed=9, attacking_rate=0.1, learn_from_rate=-1, train=2,
+                                remove_divergent=True, remove_zero=True).seed_particles()
+    s.watch(range(0, 512, 64), every=1, capacity=8)
+    s.evolve(5)
+    hp = s.historical_particles()
+    seen = 0
+    for states in hp.values():
+        for st in states:
+            if st.get('action') == 'train_self':
+                assert st['fitted'] == 2 and st['counterpart'] is None and np.isfinite(st['loss']) and st['loss'] >= 0
+                seen += 1
+    assert seen >= 30
