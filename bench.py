@@ -42,12 +42,13 @@ FLOP_PER_SELF_APP = 392.0       # 14 points x 14 MAC x 2
 FP32_INSTR_PER_SELF_APP = 224.0  # FMA-pipe lane-ops in the pinned operation order: 14 x (8 FMA + 6 MUL + 2 ADD)
 BYTES_PER_NET = 112.0           # 56 B read + 56 B write per resident episode
 # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel at 2^24 nets
-# (profiles/r01_k1_self_apply_fixed_packed_ncu_summary.csv): 940.3 MB + 880.5 MB per launch
+# (profiles/r02_k1_self_apply_fixed_ncu_summary.csv, unchanged since round 1): 0.941 GB + 0.880 GB per launch
 NCU_TRAFFIC_BYTES_PER_NET = (940.291584e6 + 880.501760e6) / (1 << 24)
-# the same for the 10 M-particle soup generation kernel (profiles/r01_soup_sync_10m_ncu.txt)
-SOUP_10M_NCU_TRAFFIC = 1.559e9
-SOUP_10M_NCU_SOURCE = ("ncu dram bytes of one launch at 10 M particles (1.01 GB read + 0.55 GB write), "
-                       "profiles/r01_soup_sync_10m_ncu.txt")
+# the same for one generation of the 10 M-particle soup = soup_lists_kernel + soup_sync_kernel + soup_deferred_learners_kernel
+# (profiles/r02_soup_sync_10m_ncu_summary.csv: 0.059 + 1.407 + 0.411 GB read + written)
+SOUP_10M_NCU_TRAFFIC = 1.877e9
+SOUP_10M_NCU_SOURCE = ("ncu dram bytes of the three launches of one generation at 10 M particles (lists 0.06 GB, tile kernel "
+                       "0.86 + 0.55 GB, deferred learners 0.34 + 0.07 GB), profiles/r02_soup_sync_10m_ncu_summary.csv")
 METRIC = "net self-applications/sec"
 UNIT = "self-applications/s"
 
@@ -377,7 +378,8 @@ def secondary_legs(eng, torch, dist, rank, world, dev, probe):
     out["soup_10m"] = {"metric": "soup generations/sec", "value": 20 / dt, "unit": "generations/s",
                        "config": dict(workload="soup_10m_ww_train0", particles=10_000_000, generations=20, **kw0),
                        "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                    "traffic": SOUP_10M_NCU_TRAFFIC, "peak_source": peak_src, "kernel": "soup_sync_kernel<WW(2,2)>",
+                                    "traffic": SOUP_10M_NCU_TRAFFIC, "peak_source": peak_src,
+                                    "kernel": "soup_sync_kernel<WW(2,2)> (+ lists and deferred-learners launches of the generation)",
                                     "algorithmic_bytes": "130 B per particle-generation (112 B own record in/out + 0.2 x 56 B "
                                                          "partner records + list heads)",
                                     "traffic_source": SOUP_10M_NCU_SOURCE}}
@@ -583,7 +585,7 @@ def main():
             "gpu_launches": K,
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": NCU_TRAFFIC_BYTES_PER_NET * n,
-                         "traffic_source": "ncu --set full, profiles/r01_k1_self_apply_fixed_packed_ncu_summary.csv "
+                         "traffic_source": "ncu --set full, profiles/r02_k1_self_apply_fixed_ncu_summary.csv "
                                            "(algorithmic bytes per launch = 112 B x nets)",
                          "kernel": "self_apply_fixed_kernel<WW(2,2)>", "kernel_ms": kern_ms,
                          "peak_source": "FFMA-only probe kernel measured live (MEASURED_PEAKS.json has no FP32 entry)",

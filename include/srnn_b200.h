@@ -181,12 +181,14 @@ int srnn_soup_sync_peers(const srnn_net_desc *d, const srnn_soup_params *p, cons
  * at every rank's int32[n_shards + 1] flag array in peer-mapped memory (zeroed once, before the first generation and
  * behind a barrier).  Behind the generation a one-warp kernel stores gen into word my_shard of every rank's array;
  * wait_gen > 0 makes the call wait -- on the device, ahead of the generation -- until this rank's array shows every
- * rank at wait_gen or later (pass gen - 1 from the second generation of a run on; generations count up, < 2^31). */
+ * rank at wait_gen or later (pass gen - 1 from the second generation of a run on; generations count up, < 2^31).
+ * scratch (local int32[shard_len + 16], nullable, no initialisation): lets the recurrent kind hand its learn_from epochs
+ * to a dense second kernel; without it everything runs inside the generation kernel. */
 int srnn_soup_chain_peers(const srnn_net_desc *d, const srnn_soup_params *p, const float *const *shards, int32_t n_shards,
                           int64_t shard_len, int32_t my_shard, int64_t ld, float *w_out, int64_t out_ld, uint64_t seed,
                           uint64_t gen, int32_t *const *heads_cur, int32_t *const *nexts_cur, int32_t *const *heads_nxt,
-                          int32_t *const *nexts_nxt, int32_t *const *flags, int64_t wait_gen, uint8_t *action, double *loss,
-                          uint8_t *dead, void *stream);
+                          int32_t *const *nexts_nxt, int32_t *const *flags, int64_t wait_gen, int32_t *scratch,
+                          uint8_t *action, double *loss, uint8_t *dead, void *stream);
 
 /* First generation of such a run: this rank's particles push their generation-`gen` attacks (Philox draws of
  * (seed, global particle, gen), code/soup.py:56-59) onto the owners' lists.  heads must be -1 on every rank beforehand. */

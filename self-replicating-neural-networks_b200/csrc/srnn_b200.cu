@@ -1102,12 +1102,18 @@ __host__ __device__ constexpr int soup_ppt() {
 template <class S>
 __host__ __device__ constexpr int soup_tile() { return SOUP_BS * soup_ppt<S>(); }   // particles per CTA
 
-template <class S, int SBS, bool CG, int QDIV = SRNN_SOUP_QDIV>
+// DEFER: the learn_from epochs are NOT run here.  The tile only lists its learners (global list, one atomic per CTA) and
+// leaves their cull test to soup_deferred_learners_kernel, a dense kernel with its own register budget.  For the recurrent
+// net, whose BPTT needs ~160 registers and sat behind this kernel's 72-register cap as 384 bytes of spills on a single
+// warp per tile, that takes a third off the generation (profiles/r02_soup_by_kind.txt).
+template <class S, int SBS, bool CG, int QDIV = SRNN_SOUP_QDIV, bool DEFER = false>
 __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const ShardTable &snap, const float *own,
                                                      int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld,
                                                      int64_t slot0, int64_t n, const SoupP &p, uint64_t seed, uint64_t gen,
                                                      const Limits &lim, const int32_t *head, const int32_t *next,
-                                                     uint8_t *action, double *loss, uint8_t *dead_out) {
+                                                     uint8_t *action, double *loss, uint8_t *dead_out,
+                                                     int32_t *defer_list = nullptr, int32_t *defer_count = nullptr) {
+    static_assert(!(DEFER && CG), "deferred learners: not in the persistent kernel");
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int NW = S::NW, PPT = soup_ppt<S>(), TILE = SBS * PPT;
     constexpr int QCAP = TILE / QDIV / 4 * 4;   // partner records prefetched per phase and tile (mean TILE/10); beyond: slow path
@@ -1117,7 +1123,7 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     __shared__ int32_t lrn_s[TILE];
     __shared__ uint16_t queue[TILE], queue_l[TILE];
     __shared__ int32_t nxt_s[QCAP];     // second attacker of each queued victim (-1: the usual single attacker)
-    __shared__ int q_len, ql_len;
+    __shared__ int q_len, ql_len, dl_base;
     const int tid = threadIdx.x;
     const int64_t base = tile_idx * TILE;
     const int sev = p.severity > 0 ? p.severity : 0, tr = p.train > 0 ? p.train : 0;
@@ -1153,11 +1159,12 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
         if (ASYNC && lr[r] >= 0 && sev > 0) {
             const int ql = atomicAdd(&ql_len, 1);
             queue_l[ql] = (uint16_t)v;
-            if (prefetch && ql < QCAP) record_copy_async<NW>(tch_s + ql * NW, shard_record(snap, snap_ld, lr[r]));
+            if (!DEFER && prefetch && ql < QCAP) record_copy_async<NW>(tch_s + ql * NW, shard_record(snap, snap_ld, lr[r]));
         }
     }
     if (ASYNC) async_copy_wait();
     __syncthreads();
+    if (DEFER && tid == 0 && ql_len > 0) dl_base = atomicAdd(defer_count, ql_len);   // visible after the next barrier
     // ---- owners enqueue their events and, in the memory-latency-bound regime (no self-training in the generation),
     //      PREFETCH the partner records into shared memory: one DRAM round trip for attackers and teachers together
     //      instead of one per serial phase (-9 % at 10 M particles; with training the extra instructions cost more
@@ -1211,7 +1218,10 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     __syncthreads();
     // ---- phase 2: learn_from x severity (code/soup.py:62-68), teacher read from the snapshot.  (Running the learners
     //      that are not attacked BEFORE phase 1, under the attackers' gathers, was measured slower: 0.585 -> 0.598 ms.)
-    for (int q = tid; q < ql_len; q += SBS) {
+    if (DEFER) {
+        for (int q = tid; q < ql_len; q += SBS) defer_list[dl_base + q] = (int32_t)(base + queue_l[q]);
+    }
+    for (int q = tid; q < (DEFER ? 0 : ql_len); q += SBS) {
         const int v = queue_l[q];
         float cur[NW];
         tile_get<NW>(tile, v, cur);
@@ -1243,15 +1253,16 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
         if (i < n) {
             float cur[NW];
             tile_get<NW>(tile, v, cur);
-            for (int e = 0; e < tr; ++e) {
+            for (int e = 0; e < (DEFER ? 0 : tr); ++e) {   // (the deferring build is only launched for generations without training)
 #pragma unroll
                 for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = cur[k];
                 if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + i), ep + (uint64_t)(sev + e), sc.ord, sc.stride);
                 ls[r] = train_epoch<S>(cur, sc, ordered, p.lr);
             }
             if (tr > 0) tile_put<NW>(tile, v, cur);
-            if (p.remove_divergent && is_diverged<NW>(cur)) dead[r] = SRNN_ACT_DIV_DEAD;
-            if (p.remove_zero && is_zero<NW>(cur, p.eps.le)) dead[r] = SRNN_ACT_ZERO_DEAD;
+            const bool deferred = DEFER && lr[r] >= 0 && sev > 0;   // its cull test follows its learn_from, elsewhere
+            if (!deferred && p.remove_divergent && is_diverged<NW>(cur)) dead[r] = SRNN_ACT_DIV_DEAD;
+            if (!deferred && p.remove_zero && is_zero<NW>(cur, p.eps.le)) dead[r] = SRNN_ACT_ZERO_DEAD;
         }
     }
     if (tid == 0) q_len = 0;
@@ -1290,15 +1301,72 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
     tile_stage_out<NW, SBS, TILE>(w_out, out_ld, base, n, tile);
 }
 
-template <class S, int SBS, int MB>
+template <class S, int SBS, int MB, bool DEFER = false>
 __global__ void __launch_bounds__(SBS, MB) soup_sync_kernel(ShardTable snap, const float *__restrict__ own, int64_t snap_ld,
                                                        int64_t n_total, float *__restrict__ w_out, int64_t out_ld,
                                                        int64_t slot0, int64_t n, SoupP p, uint64_t seed, uint64_t gen,
                                                        Limits lim, const int32_t *__restrict__ head,
                                                        const int32_t *__restrict__ next, uint8_t *action,
-                                                       double *loss, uint8_t *dead_out) {
-    soup_tile_generation<S, SBS, false, soup_qdiv(MB)>(blockIdx.x, snap, own, snap_ld, n_total, w_out, out_ld, slot0, n, p, seed, gen, lim,
-                                        head, next, action, loss, dead_out);
+                                                       double *loss, uint8_t *dead_out, int32_t *defer_list,
+                                                       int32_t *defer_count) {
+    soup_tile_generation<S, SBS, false, soup_qdiv(MB), DEFER>(blockIdx.x, snap, own, snap_ld, n_total, w_out, out_ld, slot0, n, p,
+                                                              seed, gen, lim, head, next, action, loss, dead_out, defer_list,
+                                                              defer_count);
+}
+// which kinds hand their learn_from epochs to the dense kernel below (when the generation has no self-training, whose
+// epochs would have to follow the learn_from of the same particle)
+// Measured (generation of 3.3 M / 10 M particles, attack 0.1 + learn_from 0.1, ms): RNN 0.463 -> 0.303, WW 0.192 -> 0.175 /
+// 0.535 -> 0.476; AGG 0.204 -> 0.211 (its SGD is one 4-value sample: cheaper inside the tile than a second pass)
+template <class S> constexpr bool soup_defers_learning() { return S::KIND != SRNN_KIND_AGG; }
+
+// The deferred learners of a generation, one thread each, densely: the record the tile kernel left in w_out (after the
+// attacks on it), the teacher's start-of-generation record, learn_from x severity, then the cull tests and the respawn
+// that the tile kernel skipped for them (code/soup.py:62-68, 77-86).
+template <class S>
+__global__ void __launch_bounds__(BS) soup_deferred_learners_kernel(ShardTable snap, int64_t snap_ld, int64_t n_total,
+                                                                    float *w_out, int64_t out_ld, int64_t slot0, SoupP p,
+                                                                    uint64_t seed, uint64_t gen, Limits lim,
+                                                                    const int32_t *__restrict__ learners,
+                                                                    const int32_t *__restrict__ count, uint8_t *action,
+                                                                    uint8_t *dead_out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    SgdScratch sc = sgd_scratch<S>(smem, BS);
+    __syncthreads();  // position codes visible
+    const int m = *count;
+    const int sev = p.severity > 0 ? p.severity : 0;
+    const uint64_t ep = gen * (uint64_t)sev;               // train == 0 in this mode
+    const bool ordered = S::NS > 1 && p.perm_mode == SRNN_PERM_PHILOX;
+    for (int64_t t = (int64_t)blockIdx.x * BS + threadIdx.x; t < m; t += (int64_t)gridDim.x * BS) {
+        const int64_t l = learners[t];
+        float cur[S::NW];
+        {
+            const float *rec = w_out + l * out_ld;
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) cur[k] = rec[k];
+        }
+        int64_t at, lr;
+        soup_draw(p, seed, (uint64_t)(slot0 + l), gen, n_total, &at, &lr);
+        {
+            float tch[S::NW];
+            record_get_uniform<S::NW, LD_RO>(shard_record(snap, snap_ld, lr), tch);
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) sc.tgt[k * sc.stride] = tch[k];
+        }
+        for (int e = 0; e < sev; ++e) {
+            if (ordered) philox_perm<S::NS>(seed, (uint64_t)(slot0 + l), ep + (uint64_t)e, sc.ord, sc.stride);
+            train_epoch<S>(cur, sc, ordered, p.lr);
+        }
+        int dead = 0;
+        if (p.remove_divergent && is_diverged<S::NW>(cur)) dead = SRNN_ACT_DIV_DEAD;
+        if (p.remove_zero && is_zero<S::NW>(cur, p.eps.le)) dead = SRNN_ACT_ZERO_DEAD;
+        if (dead) {
+            log_dying<S::NW>(p, slot0 + l, cur);
+            init_net<S>(seed, (uint64_t)(slot0 + l), (uint32_t)gen, lim, cur);
+        }
+        record_store<S::NW>(w_out, out_ld, l, cur);
+        if (action) action[l] = dead ? (uint8_t)dead : (uint8_t)SRNN_ACT_LEARN;
+        if (dead_out) dead_out[l] = dead ? 1 : 0;
+    }
 }
 
 // Chained variant for srnn_soup_sync_run (unsharded, many generations): ONE launch per generation.  After its tile
@@ -1357,13 +1425,14 @@ __device__ __forceinline__ void push_attack(const SoupP &p, uint64_t seed, int64
         t.next[r][g] = old;
     }
 }
-template <class S, int SBS, int MB>
+template <class S, int SBS, int MB, bool DEFER = false>
 __global__ void __launch_bounds__(SBS, MB) soup_chain_peers_kernel(ShardTable snap, const float *__restrict__ own,
                                                                    int64_t ld, int64_t n_total, float *__restrict__ w_out,
                                                                    int64_t out_ld, int64_t slot0, int64_t n, SoupP p,
                                                                    uint64_t seed, uint64_t gen, Limits lim, int32_t *head_cur,
                                                                    const int32_t *next_cur, PeerListTable nxt, int make_next,
-                                                                   uint8_t *action, double *loss, uint8_t *dead_out) {
+                                                                   uint8_t *action, double *loss, uint8_t *dead_out,
+                                                                   int32_t *defer_list, int32_t *defer_count) {
     // Generation g+1's pushes go FIRST: the exchange on the victim owner's head word is a round trip over NVLink, and
     // issued here it travels under the whole tile generation instead of holding the finished CTA on the SM (at the tail
     // it cost 15 % at 2 GPUs).  Only the returned previous head has to be kept until the store below.
@@ -1385,8 +1454,9 @@ __global__ void __launch_bounds__(SBS, MB) soup_chain_peers_kernel(ShardTable sn
             }
         }
     }
-    soup_tile_generation<S, SBS, false, soup_qdiv(MB)>(blockIdx.x, snap, own, ld, n_total, w_out, out_ld, slot0, n, p, seed, gen,
-                                                       lim, head_cur, next_cur, action, loss, dead_out);
+    soup_tile_generation<S, SBS, false, soup_qdiv(MB), DEFER>(blockIdx.x, snap, own, ld, n_total, w_out, out_ld, slot0, n, p, seed,
+                                                              gen, lim, head_cur, next_cur, action, loss, dead_out, defer_list,
+                                                              defer_count);
 #pragma unroll
     for (int r = 0; r < PPT; ++r) {
         const int64_t i = (int64_t)blockIdx.x * soup_tile<S>() + threadIdx.x + r * SBS;
@@ -2065,6 +2135,65 @@ static bool ranges_overlap(const float *a, int64_t na, int64_t lda, const float 
     return a0 < b1 && b0 < a1;
 }
 
+extern "C++" {
+template <class S>
+static int launch_deferred_learners(const ShardTable &tab, int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld,
+                                    int64_t slot0, int64_t n, const SoupP &q, uint64_t seed, uint64_t gen, const Limits &lim,
+                                    const int32_t *list, const int32_t *count, uint8_t *action, uint8_t *dead, cudaStream_t st) {
+    const size_t sm = sgd_smem_bytes<S>(BS);
+    int rc = allow_smem(soup_deferred_learners_kernel<S>, sm);
+    if (rc) return rc;
+    // sized for the expected number of learners (rate x n) with head-room; the kernel strides over whatever there is
+    const double expect = (q.learn_from_rate < 1.0 ? q.learn_from_rate : 1.0) * (double)n * 1.25 + 4096.0;
+    const int64_t want = std::min<int64_t>(n, (int64_t)expect);
+    soup_deferred_learners_kernel<S><<<grid_for(want), BS, sm, st>>>(tab, snap_ld, n_total, w_out, out_ld, slot0, q, seed, gen,
+                                                                      lim, list, count, action, dead);
+    return SRNN_OK;
+}
+// (function templates so that `if constexpr` really discards the DEFER instantiations of the kinds that do not defer)
+template <class S>
+static int try_deferred_sync(bool *done, const ShardTable &tab, const float *own, int64_t snap_ld, int64_t n_total, float *w_out,
+                             int64_t out_ld, int64_t slot0, int64_t n, const SoupP &q, uint64_t seed, uint64_t gen,
+                             const Limits &lim, const int32_t *head, const int32_t *next, uint8_t *action, double *loss,
+                             uint8_t *dead, int32_t *dl, int32_t *dc, unsigned grid, size_t sm, cudaStream_t st) {
+    *done = false;
+    if constexpr (soup_defers_learning<S>()) {
+        if (dl && q.learn_from_rate > 0.0 && q.severity > 0 && q.train <= 0 && n >= SOUP_DENSE_MIN) {
+            cudaError_t ce = cudaMemsetAsync(dc, 0, sizeof(int32_t), st);
+            if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+            soup_sync_kernel<S, SOUP_BS, SRNN_SOUP_MINB, true><<<grid, SOUP_BS, sm, st>>>(
+                tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead, dl, dc);
+            int rc = launch_deferred_learners<S>(tab, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, dl, dc, action,
+                                                 dead, st);
+            if (rc) return rc;
+            *done = true;
+        }
+    }
+    return SRNN_OK;
+}
+template <class S>
+static int try_deferred_chain(bool *done, const ShardTable &tab, const float *own, int64_t ld, int64_t n_total, float *w_out,
+                              int64_t out_ld, int64_t slot0, int64_t n, const SoupP &q, uint64_t seed, uint64_t gen,
+                              const Limits &lim, int32_t *head_cur, const int32_t *next_cur, const PeerListTable &nxt,
+                              int make_next, uint8_t *action, double *loss, uint8_t *dead, int32_t *dl, int32_t *dc,
+                              unsigned grid, size_t sm, cudaStream_t st) {
+    *done = false;
+    if constexpr (soup_defers_learning<S>()) {
+        if (dl && q.learn_from_rate > 0.0 && q.severity > 0 && q.train <= 0 && n >= SOUP_DENSE_MIN) {
+            cudaError_t ce = cudaMemsetAsync(dc, 0, sizeof(int32_t), st);
+            if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+            soup_chain_peers_kernel<S, SOUP_BS, SRNN_SOUP_MINB, true><<<grid, SOUP_BS, sm, st>>>(
+                tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, nxt, make_next, action, loss,
+                dead, dl, dc);
+            int rc = launch_deferred_learners<S>(tab, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, dl, dc, action, dead, st);
+            if (rc) return rc;
+            *done = true;
+        }
+    }
+    return SRNN_OK;
+}
+}  // extern "C++"
+
 static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, const ShardTable &tab, const float *own,
                           int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld, int64_t slot0, int64_t n,
                           uint64_t seed, uint64_t gen, int32_t *scratch, uint8_t *action, double *loss, uint8_t *dead,
@@ -2115,12 +2244,17 @@ static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, con
     constexpr int SBS = SOUP_BS;                                                                             \
     const size_t sm = sgd_smem_bytes<S>(SBS);                                                                \
     const unsigned grid = (unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>());                             \
-    if (n >= SOUP_DENSE_MIN)                                                                                 \
+    bool deferred_ = false;                                                                                  \
+    rc = try_deferred_sync<S>(&deferred_, tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, \
+                              action, loss, dead, next + n_total + n, scratch + n_total + 4 * n + 8, grid, sm, st); \
+    if (rc) return rc;                                                                                       \
+    if (deferred_) { }                                                                                       \
+    else if (n >= SOUP_DENSE_MIN)                                                                            \
         soup_sync_kernel<S, SBS, SRNN_SOUP_MINB><<<grid, SBS, sm, (cudaStream_t)stream>>>(                   \
-            tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead); \
+            tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead, nullptr, nullptr); \
     else                                                                                                     \
         soup_sync_kernel<S, SBS, SOUP_MINB_SMALL><<<grid, SBS, sm, (cudaStream_t)stream>>>(                  \
-            tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead);
+            tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead, nullptr, nullptr);
     SRNN_DISPATCH(d)
 #undef BODY
     return check_launch("srnn_soup_sync");
@@ -2247,8 +2381,8 @@ int srnn_soup_push_lists(const srnn_soup_params *p, int32_t n_shards, int64_t sh
 int srnn_soup_chain_peers(const srnn_net_desc *d, const srnn_soup_params *p, const float *const *shards, int32_t n_shards,
                           int64_t shard_len, int32_t my_shard, int64_t ld, float *w_out, int64_t out_ld, uint64_t seed,
                           uint64_t gen, int32_t *const *heads_cur, int32_t *const *nexts_cur, int32_t *const *heads_nxt,
-                          int32_t *const *nexts_nxt, int32_t *const *flags, int64_t wait_gen, uint8_t *action, double *loss,
-                          uint8_t *dead, void *stream) {
+                          int32_t *const *nexts_nxt, int32_t *const *flags, int64_t wait_gen, int32_t *scratch,
+                          uint8_t *action, double *loss, uint8_t *dead, void *stream) {
     if (!d || !shards || !w_out || !heads_cur || !nexts_cur) return fail(SRNN_ERR_ARG, "a required pointer is NULL%s");
     if (gen >= 0x7fffffffULL && flags) return fail(SRNN_ERR_ARG, "fused signalling needs gen < 2^31%s");
     if (n_shards < 1 || n_shards > SRNN_MAX_SHARDS || my_shard < 0 || my_shard >= n_shards)
@@ -2298,12 +2432,18 @@ int srnn_soup_chain_peers(const srnn_net_desc *d, const srnn_soup_params *p, con
     constexpr int SBS = SOUP_BS;                                                                             \
     const size_t sm = sgd_smem_bytes<S>(SBS);                                                                \
     const unsigned grid = (unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>());                             \
-    if (n >= SOUP_DENSE_MIN)                                                                                 \
+    bool deferred_ = false;                                                                                  \
+    rc = try_deferred_chain<S>(&deferred_, tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, \
+                               nxt, make_next, action, loss, dead, scratch, scratch ? scratch + n + 8 : nullptr, grid, sm, \
+                               (cudaStream_t)stream);                                                        \
+    if (rc) return rc;                                                                                       \
+    if (deferred_) { }                                                                                       \
+    else if (n >= SOUP_DENSE_MIN)                                                                            \
         soup_chain_peers_kernel<S, SBS, SRNN_SOUP_MINB><<<grid, SBS, sm, (cudaStream_t)stream>>>(            \
-            tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, nxt, make_next, action, loss, dead); \
+            tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, nxt, make_next, action, loss, dead, nullptr, nullptr); \
     else                                                                                                     \
         soup_chain_peers_kernel<S, SBS, SOUP_MINB_SMALL><<<grid, SBS, sm, (cudaStream_t)stream>>>(           \
-            tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, nxt, make_next, action, loss, dead);
+            tab, own, ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head_cur, next_cur, nxt, make_next, action, loss, dead, nullptr, nullptr);
     SRNN_DISPATCH(d)
 #undef BODY
     if (ft.n > 0) soup_signal_flags_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ft, my_shard, (int32_t)gen);

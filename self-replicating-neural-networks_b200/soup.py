@@ -280,10 +280,10 @@ class _CudaBackend:
         _eng.soup_push_lists(sp, n_shards, shard_len, my_shard, seed, gen, heads, nexts, stream=stream)
 
     def soup_chain_peers(self, desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur,
-                         heads_nxt, nexts_nxt, action, dead, stream=None, flags=None, wait_gen=0, loss=None):
+                         heads_nxt, nexts_nxt, action, dead, stream=None, flags=None, wait_gen=0, loss=None, scratch=None):
         _eng.soup_chain_peers(desc, sp, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur,
                               heads_nxt, nexts_nxt, action=action, dead=dead, stream=stream, flags=flags, wait_gen=wait_gen,
-                              loss=loss)
+                              loss=loss, scratch=scratch)
 
     def soup_exact(self, desc, sp_kwargs, w, seed, gen0, n_gens, scratch, action, dead, rounds, loss=None):
         sp = _eng.make_soup_params(**sp_kwargs)
@@ -593,7 +593,7 @@ class PopulationSoup:
             self.backend.soup_chain_peers(self.desc, sp, self._shard_arrays[self._cur], self.n_local, self.rank,
                                           self.desc.n_weights, self._next, self.seed, self.time, hc, nc, hn, nn,
                                           self.action, self.dead, stream=stream, flags=tabs[2], wait_gen=self.time - 1,
-                                          **self._loss_kw())
+                                          scratch=self._scratch, **self._loss_kw())
             self._lists_valid = (self.time + 1, self._lists_valid[1])
             return True
         self._pre_generation()

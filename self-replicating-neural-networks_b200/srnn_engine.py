@@ -349,7 +349,7 @@ def soup_push_lists(params, n_shards, shard_len, my_shard, seed, gen, heads, nex
 
 
 def soup_chain_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, seed, gen, heads_cur, nexts_cur, heads_nxt,
-                     nexts_nxt, action=None, loss=None, dead=None, stream=None, flags=None, wait_gen=0):
+                     nexts_nxt, action=None, loss=None, dead=None, stream=None, flags=None, wait_gen=0, scratch=None):
     """One generation of a sharded soup whose attack lists are built by the attackers' ranks: ONE launch, which also
     pushes generation gen+1's attacks (heads_nxt / nexts_nxt, None to skip).  flags / wait_gen: the fused cross-GPU
     signal that replaces the per-generation barrier (include/srnn_b200.h)."""
@@ -357,7 +357,7 @@ def soup_chain_peers(desc, params, shard_ptrs, shard_len, my_shard, ld, w_out, s
     _chk(lib().srnn_soup_chain_peers(C.byref(desc), C.byref(params), arr, C.c_int32(len(arr)), C.c_int64(shard_len),
                                      C.c_int32(my_shard), C.c_int64(ld), _ptr(w_out), C.c_int64(w_out.shape[1]),
                                      C.c_uint64(seed), C.c_uint64(gen), heads_cur, nexts_cur, heads_nxt, nexts_nxt,
-                                     flags, C.c_int64(wait_gen), _ptr(action), _ptr(loss), _ptr(dead),
+                                     flags, C.c_int64(wait_gen), _ptr(scratch), _ptr(action), _ptr(loss), _ptr(dead),
                                      _stream() if stream is None else C.c_void_p(stream.cuda_stream)))
 
 

@@ -386,6 +386,59 @@ def test_soup_chain_peers_on_one_gpu(eng, key, world):
         assert int((t[:, :shard] != -1).sum().item()) == 0       # every consumed head was reset
 
 
+@pytest.mark.parametrize("key", [(0, 2, 2, 0), (2, 2, 2, 0)])
+def test_soup_deferred_learners(eng, key):
+    """Large weightwise and recurrent soups hand their learn_from epochs to a dense second kernel
+    (soup_deferred_learners_kernel; taken from 2^19 particles per launch on, generations without self-training).  Same
+    results as the oracle's generation, bit for bit -- weights, actions, respawns -- through srnn_soup_sync (one owner
+    and two uneven owners) and through the chained sharded entry srnn_soup_chain_peers."""
+    import torch
+    dg, do = both(eng, key)
+    shard = (1 << 19) + 64
+    n = 2 * shard
+    kw = dict(attacking_rate=0.2, learn_from_rate=0.2, train=0, learn_from_severity=2, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population(key, n, seed=91)
+    ref = w.copy()
+    snap = torch.from_numpy(w).cuda()
+    scratch = torch.zeros(eng.soup_scratch_len(n, n), dtype=torch.int32, device="cuda")
+    lists = [torch.full((2, shard + n), -1, dtype=torch.int32, device="cuda") for _ in range(2)]
+    small = [torch.zeros(shard + 16, dtype=torch.int32, device="cuda") for _ in range(2)]
+
+    def tables(par):
+        return (eng.shard_ptr_array([t[par].data_ptr() for t in lists]),
+                eng.shard_ptr_array([t[par].data_ptr() + 4 * shard for t in lists]))
+    h1, n1 = tables(1)
+    for r in range(2):
+        eng.soup_push_lists(pg, 2, shard, r, 23, 1, h1, n1)
+    for gen in (1, 2):
+        out = torch.zeros_like(snap)
+        action = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        dead = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        eng.soup_sync(dg, pg, snap, n, out, 0, n, 23, gen, scratch, action=action, dead=dead)
+        rout = np.zeros_like(ref)
+        ra, _, _ = oracle.soup_sync(do, po, ref, n, rout, 0, n, 23, gen)
+        assert_same_weights(out.cpu().numpy(), rout, "gen %d" % gen)
+        assert np.array_equal(action.cpu().numpy(), ra)
+        assert np.array_equal(dead.cpu().numpy(), (ra >= 4).astype(np.uint8)) and (ra == 2).sum() > 0.1 * n
+        # two uneven owners (the second one below the threshold: it runs the learners inside the tile kernel)
+        cut = n - 5000
+        o2 = torch.zeros_like(snap)
+        eng.soup_sync(dg, pg, snap, n, o2[:cut], 0, cut, 23, gen, scratch)
+        eng.soup_sync(dg, pg, snap, n, o2[cut:], cut, n - cut, 23, gen, scratch)
+        assert torch.equal(o2.view(torch.int32), out.view(torch.int32))
+        # chained sharded entry, two shards emulated on this GPU
+        cur = [snap[:shard].clone(), snap[shard:].clone()]
+        o3 = torch.zeros_like(snap)
+        (hc, nc), (hn, nn) = tables(gen & 1), tables((gen + 1) & 1)
+        for r in range(2):
+            eng.soup_chain_peers(dg, pg, [t.data_ptr() for t in cur], shard, r, cur[0].shape[1],
+                                 o3[r * shard:(r + 1) * shard], 23, gen, hc, nc, hn, nn, scratch=small[r])
+        assert torch.equal(o3.view(torch.int32), out.view(torch.int32))
+        snap, ref = out, rout
+
+
 @pytest.mark.parametrize("key", SHAPES)
 @pytest.mark.parametrize("n", [1, 255, 256, 257, 1000])
 def test_soup_sync_every_fast_shape_and_ragged_tiles(eng, key, n):

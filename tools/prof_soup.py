@@ -15,7 +15,8 @@ path = int(sys.argv[4]) if len(sys.argv) > 4 else 0   # 0 auto, 1 fused kernel, 
 order = sys.argv[5] if len(sys.argv) > 5 else "snapshot"   # or "exact"
 ar = float(os.environ.get("PROF_ATTACK", "0.1"))   # rates overridable for phase-cost breakdowns
 lfr = float(os.environ.get("PROF_LEARN", "0.1"))
-s = PopulationSoup(eng.KIND_WW, n, seed=4, attacking_rate=ar, learn_from_rate=lfr, train=train, remove_divergent=True,
+kind = int(os.environ.get("PROF_KIND", "0"))       # 0 WW(2,2), 1 AGG(4,2,2), 2 RNN(2,2)
+s = PopulationSoup(kind, n, aggregates=4 if kind == 1 else 0, seed=4, attacking_rate=ar, learn_from_rate=lfr, train=train, remove_divergent=True,
                    remove_zero=True, epsilon=1e-4, engine_path=path, order=order).seed_particles()
 s.evolve(2)
 torch.cuda.synchronize()
@@ -24,5 +25,5 @@ e0.record()
 s.evolve(gens)
 e1.record()
 e1.synchronize()
-print("attack %g learn %g" % (ar, lfr), "particles %d train %d path %d order %s: %.3f ms / generation (rounds %d)" % (n, train, path, order,
+print("kind %d attack %g learn %g" % (kind, ar, lfr), "particles %d train %d path %d order %s: %.3f ms / generation (rounds %d)" % (n, train, path, order,
       e0.elapsed_time(e1) / gens, s.rounds), s.count())
