@@ -1087,6 +1087,9 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 // train 1: 19 vs 20 us per generation): below SOUP_DENSE_MIN particles per launch the kernels are the 6-CTA build
 // (80 registers, prefetch areas TILE/4), from there on the 7-CTA build.
 constexpr int64_t SOUP_DENSE_MIN = 1 << 19;
+// launches of at least this many particles hand learn_from to the dense second kernel; below, the extra launches cost more
+// than the tile kernel saves (mixed 10 M soup on 8 GPUs, 417 k particles per launch: 5777 generations/s without, 4897 with)
+constexpr int64_t SOUP_DEFER_MIN = 1 << 19;
 constexpr int SOUP_MINB_SMALL = 6;
 __host__ __device__ constexpr int soup_qdiv(int mb) { return mb >= 7 ? SRNN_SOUP_QDIV : 4; }
 #ifndef SRNN_SOUP_ASYNC
@@ -2158,7 +2161,7 @@ static int try_deferred_sync(bool *done, const ShardTable &tab, const float *own
                              uint8_t *dead, int32_t *dl, int32_t *dc, unsigned grid, size_t sm, cudaStream_t st) {
     *done = false;
     if constexpr (soup_defers_learning<S>()) {
-        if (dl && q.learn_from_rate > 0.0 && q.severity > 0 && q.train <= 0 && n >= SOUP_DENSE_MIN) {
+        if (dl && q.learn_from_rate > 0.0 && q.severity > 0 && q.train <= 0 && n >= SOUP_DEFER_MIN) {
             cudaError_t ce = cudaMemsetAsync(dc, 0, sizeof(int32_t), st);
             if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
             soup_sync_kernel<S, SOUP_BS, SRNN_SOUP_MINB, true><<<grid, SOUP_BS, sm, st>>>(
@@ -2179,7 +2182,7 @@ static int try_deferred_chain(bool *done, const ShardTable &tab, const float *ow
                               unsigned grid, size_t sm, cudaStream_t st) {
     *done = false;
     if constexpr (soup_defers_learning<S>()) {
-        if (dl && q.learn_from_rate > 0.0 && q.severity > 0 && q.train <= 0 && n >= SOUP_DENSE_MIN) {
+        if (dl && q.learn_from_rate > 0.0 && q.severity > 0 && q.train <= 0 && n >= SOUP_DEFER_MIN) {
             cudaError_t ce = cudaMemsetAsync(dc, 0, sizeof(int32_t), st);
             if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
             soup_chain_peers_kernel<S, SOUP_BS, SRNN_SOUP_MINB, true><<<grid, SOUP_BS, sm, st>>>(

@@ -422,7 +422,7 @@ def test_soup_deferred_learners(eng, key):
         assert_same_weights(out.cpu().numpy(), rout, "gen %d" % gen)
         assert np.array_equal(action.cpu().numpy(), ra)
         assert np.array_equal(dead.cpu().numpy(), (ra >= 4).astype(np.uint8)) and (ra == 2).sum() > 0.1 * n
-        # two uneven owners (the second one below the threshold: it runs the learners inside the tile kernel)
+        # two uneven owners (the second one is below the threshold: it runs its learners inside the tile kernel)
         cut = n - 5000
         o2 = torch.zeros_like(snap)
         eng.soup_sync(dg, pg, snap, n, o2[:cut], 0, cut, 23, gen, scratch)
