@@ -1088,8 +1088,9 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 // (80 registers, prefetch areas TILE/4), from there on the 7-CTA build.
 constexpr int64_t SOUP_DENSE_MIN = 1 << 19;
 // launches of at least this many particles hand learn_from to the dense second kernel; below, the extra launches cost more
-// than the tile kernel saves (mixed 10 M soup on 8 GPUs, 417 k particles per launch: 5777 generations/s without, 4897 with)
-constexpr int64_t SOUP_DEFER_MIN = 1 << 19;
+// than the tile kernel saves (mixed 10 M soup, generations/s without / with: 8 GPUs, 417 k particles per launch: 5777 / 4897;
+// 4 GPUs, 833 k: 3263 / 3206; 2 GPUs, 1.67 M: 2020 / 2194; 1 GPU, 3.3 M: 1363 / 1737)
+constexpr int64_t SOUP_DEFER_MIN = 1 << 20;
 constexpr int SOUP_MINB_SMALL = 6;
 __host__ __device__ constexpr int soup_qdiv(int mb) { return mb >= 7 ? SRNN_SOUP_QDIV : 4; }
 #ifndef SRNN_SOUP_ASYNC

@@ -389,12 +389,12 @@ def test_soup_chain_peers_on_one_gpu(eng, key, world):
 @pytest.mark.parametrize("key", [(0, 2, 2, 0), (2, 2, 2, 0)])
 def test_soup_deferred_learners(eng, key):
     """Large weightwise and recurrent soups hand their learn_from epochs to a dense second kernel
-    (soup_deferred_learners_kernel; taken from 2^19 particles per launch on, generations without self-training).  Same
+    (soup_deferred_learners_kernel; taken from 2^20 particles per launch on, generations without self-training).  Same
     results as the oracle's generation, bit for bit -- weights, actions, respawns -- through srnn_soup_sync (one owner
     and two uneven owners) and through the chained sharded entry srnn_soup_chain_peers."""
     import torch
     dg, do = both(eng, key)
-    shard = (1 << 19) + 64
+    shard = (1 << 20) + 64
     n = 2 * shard
     kw = dict(attacking_rate=0.2, learn_from_rate=0.2, train=0, learn_from_severity=2, remove_divergent=True,
               remove_zero=True, epsilon=1e-4, perm_mode=2)
