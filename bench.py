@@ -162,6 +162,24 @@ def headline_config(n):
             "parallelism": "population sharded by net index, no data-path collective"}
 
 
+def bind_to_numa_node(rank):
+    """Pin this process to the CPUs of NUMA node (rank mod #nodes); returns the CPU list or None."""
+    try:
+        nodes = sorted(int(d[4:]) for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit())
+        node = nodes[rank % len(nodes)]
+        cpus = []
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.extend(range(int(lo), int(hi or lo) + 1))
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -464,11 +482,20 @@ def main():
     import srnn_engine as eng
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    host_cpus = None
+    host_cpus, host_policy = None, "unbound"
     if world > 1:
-        # one process per GPU: stay on the GPU's NUMA node so the pinned staging buffers of the e2e leg are local to it
+        # one process per GPU.  Where the pinned staging buffers of the e2e leg live decides its scaling: they are
+        # first-touched by this thread, so the thread is placed before they are allocated.  SRNN_BENCH_HOST =
+        #   local      the GPU's own NUMA node (NVML affinity)
+        #   spread     rank r on NUMA node r mod (number of nodes): when every GPU hangs off the same node, that node's
+        #              memory is what 8 ranks x 1.9 GB per step saturate; half the traffic then goes through the other socket
+        #   unbound    wherever the launcher put the process
         # (N = 1 keeps every core: the cpu_baseline leg uses them all)
-        host_cpus = eng.bind_host_thread_to_gpu(local_rank)
+        host_policy = os.environ.get("SRNN_BENCH_HOST", "spread")
+        if host_policy == "local":
+            host_cpus = eng.bind_host_thread_to_gpu(local_rank)
+        elif host_policy == "spread":
+            host_cpus = bind_to_numa_node(local_rank)
         dist.init_process_group("nccl", device_id=dev)
     n = args.nets
     K, W = args.steps, args.warmup
@@ -578,7 +605,7 @@ def main():
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": headline_config(n),
             "run": {"fresh_arenas": R, "init_rng": "Philox4x32-10 glorot-uniform on the device",
-                    "host_affinity": ("GPU-local NUMA node, %d cpus" % len(host_cpus)) if host_cpus else "unbound"},
+                    "host_affinity": ("%s, %d cpus" % (host_policy, len(host_cpus))) if host_cpus else "unbound"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": n * 56 + 40,
                     "returns": "final weights of every net + the 5 class counters", "classes_last_step": e2e_classes},
