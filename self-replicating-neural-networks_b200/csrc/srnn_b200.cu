@@ -1087,6 +1087,7 @@ __device__ __forceinline__ void attack_chain(const ShardTable &snap, int64_t sna
 // train 1: 19 vs 20 us per generation): below SOUP_DENSE_MIN particles per launch the kernels are the 6-CTA build
 // (80 registers, prefetch areas TILE/4), from there on the 7-CTA build.
 constexpr int64_t SOUP_DENSE_MIN = 1 << 19;
+constexpr int64_t SOUP_ONE_WAVE_MAX = 148 * 6 * 128;   // particles that fit ONE wave of one-particle-per-thread CTAs (6 per SM)
 // launches of at least this many particles hand learn_from to the dense second kernel; below, the extra launches cost more
 // than the tile kernel saves (mixed 10 M soup, generations/s without / with: 8 GPUs, 417 k particles per launch: 5777 / 4897;
 // 4 GPUs, 833 k: 3263 / 3206; 2 GPUs, 1.67 M: 2020 / 2194; 1 GPU, 3.3 M: 1363 / 1737)
@@ -1110,7 +1111,7 @@ __host__ __device__ constexpr int soup_tile() { return SOUP_BS * soup_ppt<S>(); 
 // leaves their cull test to soup_deferred_learners_kernel, a dense kernel with its own register budget.  For the recurrent
 // net, whose BPTT needs ~160 registers and sat behind this kernel's 72-register cap as 384 bytes of spills on a single
 // warp per tile, that takes a third off the generation (profiles/r02_soup_by_kind.txt).
-template <class S, int SBS, bool CG, int QDIV = SRNN_SOUP_QDIV, bool DEFER = false>
+template <class S, int SBS, bool CG, int QDIV = SRNN_SOUP_QDIV, bool DEFER = false, int PPT_ = soup_ppt<S>()>
 __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const ShardTable &snap, const float *own,
                                                      int64_t snap_ld, int64_t n_total, float *w_out, int64_t out_ld,
                                                      int64_t slot0, int64_t n, const SoupP &p, uint64_t seed, uint64_t gen,
@@ -1119,7 +1120,7 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
                                                      int32_t *defer_list = nullptr, int32_t *defer_count = nullptr) {
     static_assert(!(DEFER && CG), "deferred learners: not in the persistent kernel");
     extern __shared__ __align__(16) unsigned char smem[];
-    constexpr int NW = S::NW, PPT = soup_ppt<S>(), TILE = SBS * PPT;
+    constexpr int NW = S::NW, PPT = PPT_, TILE = SBS * PPT;
     constexpr int QCAP = TILE / QDIV / 4 * 4;   // partner records prefetched per phase and tile (mean TILE/10); beyond: slow path
     __shared__ __align__(16) float tile[TILE * NW];
     __shared__ __align__(16) float att_s[QCAP * NW];   // the first attacker's record of each queued victim
@@ -1376,7 +1377,9 @@ __global__ void __launch_bounds__(BS) soup_deferred_learners_kernel(ShardTable s
 // Chained variant for srnn_soup_sync_run (unsharded, many generations): ONE launch per generation.  After its tile
 // generation every thread resets its own list head (consumed) and threads next generation's attack into the OTHER
 // pair of list arrays, so the memset and the separate lists kernel of the per-generation path disappear.
-template <class S, int SBS, int MB>
+// PPT = particles per thread.  Soups that do not fill the GPU (one wave of CTAs) are bound by the latency of a tile, and a
+// thread that trains two particles one after the other doubles the longest phase: they run one particle per thread.
+template <class S, int SBS, int MB, int PPT = soup_ppt<S>()>
 __global__ void __launch_bounds__(SBS, MB) soup_chain_kernel(const float *__restrict__ src, int64_t ld,
                                                                         float *__restrict__ dst, int64_t n, SoupP p,
                                                                         uint64_t seed, uint64_t gen, Limits lim,
@@ -1387,11 +1390,11 @@ __global__ void __launch_bounds__(SBS, MB) soup_chain_kernel(const float *__rest
     tab.base[0] = src;
     tab.len = n;
     tab.n = 1;
-    soup_tile_generation<S, SBS, false, soup_qdiv(MB)>(blockIdx.x, tab, src, ld, n, dst, ld, 0, n, p, seed, gen, lim, head_cur, next_cur,
-                                        action, nullptr, dead_out);
+    soup_tile_generation<S, SBS, false, soup_qdiv(MB), false, PPT>(blockIdx.x, tab, src, ld, n, dst, ld, 0, n, p, seed, gen, lim,
+                                                                   head_cur, next_cur, action, nullptr, dead_out);
 #pragma unroll
-    for (int r = 0; r < soup_ppt<S>(); ++r) {
-        const int64_t i = (int64_t)blockIdx.x * soup_tile<S>() + threadIdx.x + r * SBS;
+    for (int r = 0; r < PPT; ++r) {
+        const int64_t i = (int64_t)blockIdx.x * (SBS * PPT) + threadIdx.x + r * SBS;
         if (i < n) {
             head_cur[i] = -1;   // only this CTA reads its heads, and it is done with them
             if (make_next && p.attacking_rate > 0.0) {
@@ -2589,6 +2592,9 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
     const unsigned grid = (unsigned)((n + soup_tile<S>() - 1) / soup_tile<S>());                             \
     if (n >= SOUP_DENSE_MIN)                                                                                 \
         soup_chain_kernel<S, SBS, SRNN_SOUP_MINB><<<grid, SBS, sgd_smem_bytes<S>(SBS), st>>>(                \
+            src, ld, dst, n, q, seed, gen, lim, hc, nc, hn, nn, last ? action : nullptr, last ? dead : nullptr, last ? 0 : 1); \
+    else if (n <= SOUP_ONE_WAVE_MAX && q.train > 0)                                                          \
+        soup_chain_kernel<S, SBS, SOUP_MINB_SMALL, 1><<<(unsigned)((n + SBS - 1) / SBS), SBS, sgd_smem_bytes<S>(SBS), st>>>( \
             src, ld, dst, n, q, seed, gen, lim, hc, nc, hn, nn, last ? action : nullptr, last ? dead : nullptr, last ? 0 : 1); \
     else                                                                                                     \
         soup_chain_kernel<S, SBS, SOUP_MINB_SMALL><<<grid, SBS, sgd_smem_bytes<S>(SBS), st>>>(               \
