@@ -18,7 +18,9 @@
  *    committed Keras trajectories (DESIGN.md "Pinned arithmetic").
  *  - net shapes: the benchmarked ones are compile-time instantiated (fast path); every other shape with at most
  *    SRNN_MAX_WEIGHTS weights runs the per-net operations (init, apply, forward, self_apply, classify, train) on
- *    a generic run-time-shape path; srnn_kfv and srnn_soup_* exist for instantiated shapes only (SRNN_ERR_SHAPE).
+ *    a generic run-time-shape path, and so do srnn_kfv, srnn_soup_sync, srnn_soup_sync_peers and srnn_soup_sync_run
+ *    (one generic generation per call); srnn_soup_ordered, srnn_soup_exact* and srnn_soup_chain_peers exist for
+ *    the instantiated shapes only (SRNN_ERR_SHAPE).
  *    srnn_shape_supported(): 1 = instantiated, 2 = generic path, 0 = invalid.
  */
 #ifndef SRNN_B200_H

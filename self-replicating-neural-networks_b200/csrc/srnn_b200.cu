@@ -1909,6 +1909,127 @@ static int allow_smem(K kernel, size_t bytes) {
 
 }  // namespace srnn
 
+// ---------------------------------------------------------------------------------------------- run-time-shape soups + KFV
+// Population-scale Soup.evolve and the known-fixpoint sweep for ANY shape that fits SRNN_MAX_WEIGHTS:
+// one thread per particle / trial, run-time loops over the layer table, same pinned arithmetic and the same Philox
+// functions as the templated kernels -- bit-identical to the oracle, not tuned (the instantiated shapes keep the fast path).
+namespace srnn {
+namespace gen {
+__device__ inline void log_dying_dyn(const SoupP &p, int nw, int64_t global_index, const float *rec) {
+    if (!p.dying_count) return;
+    const int pos = atomicAdd(p.dying_count, 1);
+    if (pos < p.dying_cap) {
+        p.dying_idx[pos] = global_index;
+        for (int k = 0; k < nw; ++k) p.dying_w[(int64_t)pos * nw + k] = rec[k];
+    }
+}
+// one snapshot-synchronous generation for particles [slot0, slot0 + n): the particle's whole turn in one thread
+// (code/soup.py:55-87 seen from the particle: attacks on it in ascending attacker index, learn_from, train, cull, respawn)
+__global__ void __launch_bounds__(GBS) soup_sync_kernel(DynShape s, ShardTable snap, int64_t snap_ld, int64_t n_total, float *w_out,
+                                                       int64_t out_ld, int64_t slot0, int64_t n, SoupP p, uint64_t seed,
+                                                       uint64_t gen, const int32_t *__restrict__ head,
+                                                       const int32_t *__restrict__ next, uint8_t *action, double *loss,
+                                                       uint8_t *dead_out) {
+    const int64_t i = (int64_t)blockIdx.x * GBS + threadIdx.x;
+    if (i >= n) return;
+    const int nw = s.n_weights, ns = s.n_samples;
+    float cur[MAXW], oth[MAXW], res[MAXW];
+    {
+        const float *rec = shard_record(snap, snap_ld, slot0 + i);
+        for (int k = 0; k < nw; ++k) cur[k] = __ldg(rec + k);
+    }
+    int32_t last = -1;
+    for (;;) {   // the attackers of this particle, ascending
+        int32_t best = 0x7fffffff, larger = 0;
+        for (int32_t a = head[i]; a >= 0; a = next[a])
+            if (a > last) { ++larger; if (a < best) best = a; }
+        if (larger == 0) break;
+        const float *rec = shard_record(snap, snap_ld, best);
+        for (int k = 0; k < nw; ++k) oth[k] = __ldg(rec + k);
+        net_apply(s, oth, cur, res);
+        for (int k = 0; k < nw; ++k) cur[k] = res[k];
+        if (larger == 1) break;
+        last = best;
+    }
+    int64_t at, lr;
+    soup_draw(p, seed, (uint64_t)(slot0 + i), gen, n_total, &at, &lr);
+    uint8_t act = at >= 0 ? SRNN_ACT_ATTACK : SRNN_ACT_NONE;
+    const int sev = p.severity > 0 ? p.severity : 0, tr = p.train > 0 ? p.train : 0;
+    const uint64_t ep = gen * (uint64_t)(sev + tr);
+    const bool ordered = ns > 1 && p.perm_mode == SRNN_PERM_PHILOX;
+    uint8_t ord[MAXW];
+    double ls = nan("");
+    if (lr >= 0 && sev > 0) {
+        const float *rec = shard_record(snap, snap_ld, lr);
+        for (int k = 0; k < nw; ++k) oth[k] = __ldg(rec + k);
+        for (int e = 0; e < sev; ++e) {
+            if (ordered) philox_perm(seed, (uint64_t)(slot0 + i), ep + (uint64_t)e, ns, ord);
+            train_epoch(s, cur, oth, ordered ? ord : nullptr, p.lr);
+        }
+    }
+    if (lr >= 0) act = SRNN_ACT_LEARN;
+    for (int e = 0; e < tr; ++e) {
+        for (int k = 0; k < nw; ++k) oth[k] = cur[k];
+        if (ordered) philox_perm(seed, (uint64_t)(slot0 + i), ep + (uint64_t)(sev + e), ns, ord);
+        ls = train_epoch(s, cur, oth, ordered ? ord : nullptr, p.lr);
+        act = SRNN_ACT_TRAIN;
+    }
+    int dead = 0;
+    if (p.remove_divergent && is_diverged(cur, nw)) dead = SRNN_ACT_DIV_DEAD;
+    if (p.remove_zero && is_zero(cur, nw, p.eps.le)) dead = SRNN_ACT_ZERO_DEAD;
+    if (dead) {
+        log_dying_dyn(p, nw, slot0 + i, cur);
+        init_net(s, seed, (uint64_t)(slot0 + i), (uint32_t)gen, cur);
+        act = (uint8_t)dead;
+    }
+    store_rec(w_out, out_ld, i, nw, cur);
+    if (action) action[i] = act;
+    if (loss) loss[i] = ls;
+    if (dead_out) dead_out[i] = dead ? 1 : 0;
+}
+// known-fixpoint-variation trial loop (code/setups/known-fixpoint-variation.py:37-46, 60-89), run-time shape
+__global__ void __launch_bounds__(GBS) kfv_kernel(DynShape s, BaseNet basenet, int64_t n, double scale, uint32_t level, int max_steps,
+                                                 Eps eps, uint64_t seed, uint64_t slot0, int *__restrict__ ys,
+                                                 int *__restrict__ zs, unsigned long long *hist, float *__restrict__ w_out,
+                                                 int64_t ld) {
+    const int64_t i = (int64_t)blockIdx.x * GBS + threadIdx.x;
+    if (i >= n) return;
+    const int nw = s.n_weights;
+    float cur[MAXW], nxt[MAXW];
+    for (int k = 0; k < nw; k += 2) {   // one Philox block per two weights
+        const U4 x = rng4(seed, ST_KFV, slot0 + (uint64_t)i, level, (uint32_t)(k >> 1));
+        const double m0 = __dmul_rn(u01d(x.y), scale), b0 = (double)basenet.v[k];
+        cur[k] = (float)(u01d(x.x) < 0.5 ? __dadd_rn(b0, m0) : __dsub_rn(b0, m0));
+        if (k + 1 < nw) {
+            const double m1 = __dmul_rn(u01d(x.w), scale), b1 = (double)basenet.v[k + 1];
+            cur[k + 1] = (float)(u01d(x.z) < 0.5 ? __dadd_rn(b1, m1) : __dsub_rn(b1, m1));
+        }
+    }
+    int tts = 0, taf = 0;
+    bool still = true;
+    net_apply(s, cur, cur, nxt);
+    for (int st = 0; st < max_steps; ++st) {
+        for (int k = 0; k < nw; ++k) cur[k] = nxt[k];
+        if (is_zero(cur, nw, eps.le) || is_diverged(cur, nw)) break;
+        net_apply(s, cur, cur, nxt);
+        if (is_close(nxt, cur, nw, eps.ge)) {
+            if (still) ++taf;
+            else still = true;
+        } else {
+            still = false;
+        }
+        ++tts;
+    }
+    if (ys) ys[i] = tts;
+    if (zs) zs[i] = taf;
+    if (w_out) store_rec(w_out, ld, i, nw, cur);
+    if (hist) {
+        atomicAdd(&hist[tts], 1ull);
+        atomicAdd(&hist[(max_steps + 1) + taf], 1ull);
+    }
+}
+}  // namespace gen
+}  // namespace srnn
 using namespace srnn;
 
 extern "C" {
@@ -2110,7 +2231,13 @@ int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double s
         bn, n, scale, level, max_steps, e, seed, slot0, \
                                                                 time_to_vergence, time_as_fixpoint,           \
                                                                 (unsigned long long *)hist, w_out, ld);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (w_out && ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");
+        memcpy(bn.v, base_host, sizeof(float) * dyn.n_weights);
+        gen::kfv_kernel<<<ggrid(n), gen::GBS, 0, (cudaStream_t)stream>>>(dyn, bn, n, scale, level, max_steps, e, seed, slot0,
+                                                                         time_to_vergence, time_as_fixpoint,
+                                                                         (unsigned long long *)hist, w_out, ld);
+    })
 #undef BODY
     return check_launch("srnn_kfv");
 }
@@ -2218,7 +2345,8 @@ static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, con
     cudaError_t ce = cudaMemsetAsync(head, 0xFF, sizeof(int32_t) * (size_t)n, st);
     if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
     if (q.path < 0 || q.path > 3) return fail(SRNN_ERR_ARG, "engine_path must be 0..3%s");
-    const bool multipass = q.path == 2 || (q.path == 0 && n >= SOUP_MULTIPASS_MIN);
+    const bool fast_shape = srnn_shape_supported(d) == 1;
+    const bool multipass = fast_shape && (q.path == 2 || (q.path == 0 && n >= SOUP_MULTIPASS_MIN));
     if (multipass) {
         int32_t *victims = next + n_total, *learners = victims + n;
         uint8_t *flags = reinterpret_cast<uint8_t *>(learners + n);
@@ -2262,7 +2390,11 @@ static int soup_sync_impl(const srnn_net_desc *d, const srnn_soup_params *p, con
     else                                                                                                     \
         soup_sync_kernel<S, SBS, SOUP_MINB_SMALL><<<grid, SBS, sm, (cudaStream_t)stream>>>(                  \
             tab, own, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, lim, head, next, action, loss, dead, nullptr, nullptr);
-    SRNN_DISPATCH(d)
+    SRNN_DISPATCH_OR_GENERIC(d, {
+        if (snap_ld < dyn.n_weights || out_ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");
+        gen::soup_sync_kernel<<<ggrid(n), gen::GBS, 0, st>>>(dyn, tab, snap_ld, n_total, w_out, out_ld, slot0, n, q, seed, gen, head,
+                                                            next, action, loss, dead);
+    })
 #undef BODY
     return check_launch("srnn_soup_sync");
 }
@@ -2530,7 +2662,8 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
                        void *stream) {
     if (n_gens < 0) return fail(SRNN_ERR_ARG, "n_gens < 0%s");
     if (n_gens == 0 || n <= 0) return SRNN_OK;
-    if (d && p && scratch && w_a && w_b && n <= SOUP_PERSISTENT_MAX && p->engine_path == 3) {
+    const bool fast_shape = d && srnn_shape_supported(d) == 1;   // other shapes: one generic srnn_soup_sync call per generation
+    if (fast_shape && p && scratch && w_a && w_b && n <= SOUP_PERSISTENT_MAX && p->engine_path == 3) {
         // opt-in (engine_path = 3): one cooperative launch runs all generations on the device.  Measured on a B200 it
         // buys little -- 22 vs 23.5 us per generation at 100k particles, slower at 1 M -- because a generation is bound
         // by the latency of its serial phases inside each tile, not by launch overhead; so it is not the default.
@@ -2564,7 +2697,7 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
 #undef BODY
         return check_launch("srnn_soup_sync_run (persistent)");
     }
-    if (d && p && scratch && w_a && w_b && p->engine_path == 0 && n <= SOUP_CHAIN_MAX) {
+    if (fast_shape && p && scratch && w_a && w_b && p->engine_path == 0 && n <= SOUP_CHAIN_MAX) {
         // default for small and medium soups, where launch overhead matters (20 vs 23.5 us per generation at 100k
         // particles): chained generations, one launch each -- the lists of generation g+1 are built at the end of
         // generation g.  Beyond SOUP_CHAIN_MAX the extra pairing draw per particle costs more than the launches save.

@@ -528,7 +528,8 @@ def test_empty_and_invalid_calls(eng):
                                C.c_int32(1), None, None, None, None, None) == 1
     assert lib.srnn_self_apply(C.byref(dg), p, C.c_int64(14), C.c_int64(4), C.c_int32(-1), C.c_int32(0), C.c_double(1e-4),
                                C.c_int32(1), None, None, None, None, None) == 1
-    # a shape outside SRNN_SHAPES: per-net operations work (generic path), population-only operations refuse
+    # a shape outside SRNN_SHAPES: per-net operations, snapshot soups and the KFV sweep work (generic path); the
+    # exact-order and single-thread soup entries exist for the instantiated shapes only and say so
     d2 = eng.make_desc(0, 4, 3)
     w2 = torch.zeros((4, d2.n_weights), dtype=torch.float32, device="cuda")
     assert lib.srnn_self_apply(C.byref(d2), C.c_void_p(w2.data_ptr()), C.c_int64(d2.n_weights), C.c_int64(4), C.c_int32(1),
@@ -536,7 +537,12 @@ def test_empty_and_invalid_calls(eng):
     base = np.zeros(d2.n_weights, np.float32)
     assert lib.srnn_kfv(C.byref(d2), base.ctypes.data_as(C.c_void_p), C.c_int64(4), C.c_double(0.1), C.c_uint32(0),
                         C.c_int32(10), C.c_double(1e-4), C.c_uint64(0), C.c_uint64(0), None, None, None, None,
-                        C.c_int64(d2.n_weights), None) == 2
+                        C.c_int64(d2.n_weights), None) == 0
+    sp = eng.make_soup_params()
+    att = torch.full((4,), -1, dtype=torch.int64, device="cuda")
+    assert lib.srnn_soup_ordered(C.byref(d2), C.byref(sp), C.c_void_p(w2.data_ptr()), C.c_int64(d2.n_weights), C.c_int64(4),
+                                 C.c_void_p(att.data_ptr()), C.c_void_p(att.data_ptr()), C.c_uint64(0), C.c_uint64(1), None,
+                                 None, None, None, C.c_int64(0), C.c_int32(0), None, None) == 2
     assert b"SRNN_SHAPES" in lib.srnn_last_error_string()
     torch.cuda.synchronize()
     assert float(w.abs().sum()) == 0.0
@@ -647,6 +653,72 @@ def test_generic_shapes_bitwise(eng, key):
     ref = w.copy()
     oracle.train(do, ref, 3, perm_mode=2, seed=9, teacher_w=t, teacher_idx=np.arange(n)[::-1].copy())
     assert_same_weights(pop.numpy(), ref, "learn_from")
+
+
+@pytest.mark.parametrize("key", [(0, 3, 3, 0), (1, 3, 2, 6), (2, 3, 2, 0)])
+def test_generic_shape_population_soup_and_kfv(eng, key):
+    """Population-scale soups and the known-fixpoint sweep for shapes outside SRNN_SHAPES: the generic
+    generation kernel equals the oracle bit for bit -- one owner, two uneven owners, the peer-pointer entry, the
+    multi-generation run behind PopulationSoup -- and so does the generic KFV kernel."""
+    import torch
+    import soup as soup_mod
+    dg, do = both(eng, key)
+    assert eng.shape_supported(dg) == 2
+    n = 1500
+    kw = dict(attacking_rate=0.3, learn_from_rate=0.2, train=1, learn_from_severity=2, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population(key, n, seed=52)
+    snap, ref = torch.from_numpy(w).cuda(), w.copy()
+    scratch = torch.zeros(eng.soup_scratch_len(n, n), dtype=torch.int32, device="cuda")
+    for gen in range(1, 4):
+        out = torch.zeros_like(snap)
+        action = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        loss = torch.zeros(n, dtype=torch.float64, device="cuda")
+        eng.soup_sync(dg, pg, snap, n, out, 0, n, 23, gen, scratch, action=action, loss=loss)
+        rout = np.zeros_like(ref)
+        ra, rl, _ = oracle.soup_sync(do, po, ref, n, rout, 0, n, 23, gen)
+        assert_same_weights(out.cpu().numpy(), rout, "gen %d" % gen)
+        assert np.array_equal(action.cpu().numpy(), ra)
+        gl = loss.cpu().numpy()
+        assert np.array_equal(np.isnan(gl), np.isnan(rl)) and np.array_equal(gl[~np.isnan(gl)], rl[~np.isnan(rl)])
+        half = n // 2 + 11
+        o2 = torch.zeros_like(snap)
+        eng.soup_sync(dg, pg, snap, n, o2[:half], 0, half, 23, gen, scratch)
+        eng.soup_sync(dg, pg, snap, n, o2[half:], half, n - half, 23, gen, scratch)
+        assert torch.equal(o2.view(torch.int32), out.view(torch.int32))
+        sh = [snap[:n // 2].clone(), snap[n // 2:].clone()]
+        o3 = torch.zeros_like(snap)
+        for r in range(2):
+            eng.soup_sync_peers(dg, pg, [t.data_ptr() for t in sh], n // 2, r, sh[0].shape[1],
+                                o3[r * (n // 2):(r + 1) * (n // 2)], 23, gen, scratch)
+        assert torch.equal(o3.view(torch.int32), out.view(torch.int32))
+        snap, ref = out, rout
+    # PopulationSoup: the multi-generation entry falls back to one generic generation per call
+    skw = {k: v for k, v in kw.items() if k != "perm_mode"}
+    s = soup_mod.PopulationSoup(key[0], 900, width=key[1], depth=key[2], aggregates=key[3], seed=3, **skw).seed_particles()
+    ref = s.local.numpy().copy()
+    s.evolve(3)
+    for gen in range(1, 4):
+        rout = np.zeros_like(ref)
+        oracle.soup_sync(do, po, ref, 900, rout, 0, 900, 3, gen)
+        ref = rout
+    assert_same_weights(s.local.numpy(), ref, "PopulationSoup.evolve(3)")
+    assert sum(s.count().values()) == 900
+    # known-fixpoint variation around the identity-on-the-first-input fixpoint of a weightwise net of this shape
+    if key[0] == 0:
+        base = np.zeros(do.n_weights, np.float32)
+        off = 0
+        for (r, c) in eng.layer_shapes(dg):
+            base[off] = 1.0
+            off += r * c
+        for level, scale in ((3, 1e-3), (6, 1e-6)):
+            got = eng.kfv(dg, base, 4000, scale, level, 100, 1e-4, seed=12, want_weights=True)
+            ys, zs, wout = oracle.kfv(do, base, 4000, scale, level, 100, 1e-4, seed=12, want_weights=True)
+            assert np.array_equal(got["ys"].cpu().numpy(), ys) and np.array_equal(got["zs"].cpu().numpy(), zs)
+            assert_same_weights(got["w"].cpu().numpy(), wout, "kfv level %d" % level)
+            h = got["hist"].cpu().numpy()
+            assert h[0].sum() == 4000 and (h[0] * np.arange(101)).sum() == ys.sum()
 
 
 def test_generic_shape_facade(eng):
