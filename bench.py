@@ -39,7 +39,7 @@ import numpy as np  # noqa: E402
 N_NETS = 1 << 24
 N_STEPS = 100
 FLOP_PER_SELF_APP = 392.0       # 14 points x 14 MAC x 2
-FP32_INSTR_PER_SELF_APP = 224.0  # FMA-pipe lane-ops in the pinned operation order: 14 x (8 FMA + 6 MUL + 2 ADD)
+FP32_INSTR_PER_SELF_APP = 210.0  # FMA-pipe lane-ops as issued: 7 point pairs x 15 packed instructions x 2 lanes
 BYTES_PER_NET = 112.0           # 56 B read + 56 B write per resident episode
 # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this kernel at 2^24 nets
 # (profiles/r02_k1_self_apply_fixed_ncu_summary.csv, unchanged since round 1): 0.941 GB + 0.880 GB per launch

@@ -347,12 +347,19 @@ __global__ void __launch_bounds__(BS) self_apply_fixed_kernel(float *__restrict_
     tile_load<S::NW>(w, ld, base, n, tile, a);
     if (base + threadIdx.x < n) {
         const float one = opaque_one();
+        // all applications but the last may leave zeros with either sign (ww_apply, ANYZERO): nobody sees those states,
+        // and the exact last application restores the reference's result bit for bit
         int s = 0;
-        for (; s + 2 <= n_steps; s += 2) {  // ping-pong: no register copies between steps
-            net_apply<S>(a, a, b, one);
-            net_apply<S>(b, b, a, one);
+        for (; s + 2 <= n_steps - 1; s += 2) {  // ping-pong: no register copies between steps
+            net_apply<S, true>(a, a, b, one);
+            net_apply<S, true>(b, b, a, one);
         }
-        if (s < n_steps) {
+        if (s < n_steps - 1) {
+            net_apply<S, true>(a, a, b, one);
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) a[k] = b[k];
+        }
+        if (n_steps > 0) {
             net_apply<S>(a, a, b, one);
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) a[k] = b[k];
@@ -381,11 +388,16 @@ __global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restric
         // and one more application afterwards for the classifier's fixpoint test
         const float one = opaque_one();
         int s = 0;
-        for (; s + 2 <= n_steps; s += 2) {
-            net_apply<S>(cur, cur, nxt, one);
-            net_apply<S>(nxt, nxt, cur, one);
+        for (; s + 2 <= n_steps - 1; s += 2) {   // inner steps: zeros of either sign (ww_apply, ANYZERO); last step exact
+            net_apply<S, true>(cur, cur, nxt, one);
+            net_apply<S, true>(nxt, nxt, cur, one);
         }
-        if (s < n_steps) {
+        if (s < n_steps - 1) {
+            net_apply<S, true>(cur, cur, nxt, one);
+#pragma unroll
+            for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
+        }
+        if (n_steps > 0) {
             net_apply<S>(cur, cur, nxt, one);
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
@@ -398,14 +410,23 @@ __global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restric
             if (cls_out) cls_out[i] = (uint8_t)cls;
         }
     } else if (active) {
-        net_apply<S>(cur, cur, nxt, opaque_one());  // look-ahead: is_fixpoint's application IS the next self_attack
+        const float one = opaque_one();
+        net_apply<S>(cur, cur, nxt, one);  // look-ahead: is_fixpoint's application IS the next self_attack
+        // max |w_k| of a state is reduced once, when the state is produced: it is the divergence test of is_fixpoint's
+        // result in this step and the divergence test of the net itself in the next
+        float m_cur = max_abs_nan<S::NW>(cur), m_nxt = max_abs_nan<S::NW>(nxt);
         while (it < n_steps) {
-            if (mode == SRNN_RUN_UNTIL && (is_diverged<S::NW>(cur) || is_close<S::NW>(nxt, cur, eps.ge))) break;
+            if (mode == SRNN_RUN_UNTIL &&
+                (diverged_from_max(m_cur) ||
+                 (!diverged_from_max(m_nxt) && !(max_abs_diff<S::NW>(nxt, cur) >= eps.ge))))
+                break;
 #pragma unroll
-            for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
+            for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];   // (a ping-pong of the two buffers measured 1.5 % slower here)
+            m_cur = m_nxt;
             ++it;
             if (traj) record_store_scalar<S::NW>(traj + (int64_t)(it - 1) * n * ld, ld, i, cur);
-            net_apply<S>(cur, cur, nxt, opaque_one());
+            net_apply<S>(cur, cur, nxt, one);
+            m_nxt = max_abs_nan<S::NW>(nxt);
         }
         if (steps_out) steps_out[i] = it;
         if (cls_out || counters) {
@@ -609,7 +630,9 @@ struct BaseNet { float v[SRNN_MAX_WEIGHTS]; };
 // trials of a per-warp chunk -- ballot + prefix rank, batched refills -- was measured SLOWER, 5.5e10 vs 7.2e10
 // executed self-applications/s: starting a trial costs as much as several steps and the refill logic defeats the
 // straight-line step loop.)
-template <class S>
+// ANYZERO: no weights are returned (w_out == nullptr), only step counts -- every test in the loop looks at magnitudes, so
+// the applications may leave zeros with either sign (ww_apply) and save one instruction per pair of weight points.
+template <class S, bool ANYZERO>
 __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, double scale, uint32_t level,
                                                  int max_steps, Eps eps, uint64_t seed, uint64_t slot0,
                                                  int *__restrict__ ys, int *__restrict__ zs,
@@ -636,24 +659,42 @@ __global__ void __launch_bounds__(BS) kfv_kernel(BaseNet basenet, int64_t n, dou
         }
     }
     // trial loop :69-82; after each self_attack the fixpoint test's application is the next step's result
+    // (the max |w_k| of a state is computed once, when the state is produced, and serves the fixpoint test of this step and
+    // the zero / divergence tests of the next)
+    // The two buffers swap roles every step ("cur = nxt" costs no moves): `state` is the net after the self_attack,
+    // `ahead` receives the next application.
     bool still = true;
-    net_apply<S>(cur, cur, nxt, opaque_one());
-    for (int st = 0; st < max_steps; ++st) {
-#pragma unroll
-        for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
-        if (is_zero<S::NW>(cur, eps.le) || is_diverged<S::NW>(cur)) break;
-        net_apply<S>(cur, cur, nxt, opaque_one());
-        if (is_close<S::NW>(nxt, cur, eps.ge)) {
+    const float one = opaque_one();
+    net_apply<S, ANYZERO>(cur, cur, nxt, one);
+    float m_nxt = max_abs_nan<S::NW>(nxt);
+    auto trial_step = [&](const float *state, float *ahead) -> bool {
+        if (m_nxt <= eps.le || diverged_from_max(m_nxt)) return false;
+        net_apply<S, ANYZERO>(state, state, ahead, one);
+        m_nxt = max_abs_nan<S::NW>(ahead);
+        if (!diverged_from_max(m_nxt) && !(max_abs_diff<S::NW>(ahead, state) >= eps.ge)) {
             if (still) ++taf;
             else still = true;
         } else {
             still = false;
         }
         ++tts;
+        return true;
+    };
+    bool state_in_nxt = false;
+    for (int st = 0; st < max_steps; st += 2) {
+        state_in_nxt = true;
+        if (!trial_step(nxt, cur)) break;
+        if (st + 1 >= max_steps) break;
+        state_in_nxt = false;
+        if (!trial_step(cur, nxt)) break;
     }
     if (ys) ys[i] = tts;
     if (zs) zs[i] = taf;
-    if (w_out) record_store<S::NW>(w_out, ld, i, cur);
+    if (w_out) {
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) cur[k] = state_in_nxt ? nxt[k] : cur[k];
+        record_store<S::NW>(w_out, ld, i, cur);
+    }
     if (hist) {  // a few hot bins: count in shared memory, one global atomic per non-empty bin and CTA
         atomicAdd(&hist_s[tts], 1u);
         atomicAdd(&hist_s[(max_steps + 1) + taf], 1u);
@@ -1863,6 +1904,8 @@ static int make_soup(const srnn_soup_params *p, SoupP *q) {
 // the instantiated net shapes: (kind, width, depth, aggregates)
 #ifdef SRNN_DEV_ONLY_WW22   // development builds: one shape compiles in a fraction of the time (never shipped)
 #define SRNN_SHAPES(X) X(SRNN_KIND_WW, 2, 2, 0)
+#elif defined(SRNN_DEV_ONLY_RNN22)
+#define SRNN_SHAPES(X) X(SRNN_KIND_RNN, 2, 2, 0)
 #else
 #define SRNN_SHAPES(X)                                                                               \
     X(SRNN_KIND_WW, 2, 2, 0) X(SRNN_KIND_WW, 3, 2, 0) X(SRNN_KIND_WW, 2, 3, 0) X(SRNN_KIND_WW, 2, 1, 0) \
@@ -2227,10 +2270,15 @@ int srnn_kfv(const srnn_net_desc *d, const float *base_host, int64_t n, double s
 #define BODY(S)                                                                                              \
     if (w_out && ld < S::NW) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");       \
     memcpy(bn.v, base_host, sizeof(float) * S::NW);                                                          \
-    kfv_kernel<S><<<grid_for(n), BS, hist ? sizeof(unsigned int) * 2 * (max_steps + 1) : 0, (cudaStream_t)stream>>>( \
-        bn, n, scale, level, max_steps, e, seed, slot0, \
-                                                                time_to_vergence, time_as_fixpoint,           \
-                                                                (unsigned long long *)hist, w_out, ld);
+    const size_t hsm = hist ? sizeof(unsigned int) * 2 * (max_steps + 1) : 0;                                \
+    if (w_out)                                                                                               \
+        kfv_kernel<S, false><<<grid_for(n), BS, hsm, (cudaStream_t)stream>>>(                                \
+            bn, n, scale, level, max_steps, e, seed, slot0, time_to_vergence, time_as_fixpoint,               \
+            (unsigned long long *)hist, w_out, ld);                                                          \
+    else                                                                                                     \
+        kfv_kernel<S, true><<<grid_for(n), BS, hsm, (cudaStream_t)stream>>>(                                 \
+            bn, n, scale, level, max_steps, e, seed, slot0, time_to_vergence, time_as_fixpoint,               \
+            (unsigned long long *)hist, w_out, ld);
     SRNN_DISPATCH_OR_GENERIC(d, {
         if (w_out && ld < dyn.n_weights) return fail(SRNN_ERR_ARG, "record stride ld is smaller than n_weights%s");
         memcpy(bn.v, base_host, sizeof(float) * dyn.n_weights);

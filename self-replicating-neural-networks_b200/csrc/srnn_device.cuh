@@ -176,8 +176,69 @@ SRNN_DEV void mlp_forward(const float *w, const float *x, float *y) {
 // ------------------------------------------------------------------------------------------------ operators
 // out <- f_op(in);  `out` must not alias `in` or `op`.
 // WeightwiseNeuralNetwork.apply_to_weights, code/network.py:265-279
-template <class S>
+#if SRNN_PACKED_F32X2
+// Layers L.. of the MLP for TWO weight points at once: lane = point, the kernel entries are scalar operands the
+// hardware broadcasts (SASS `.F32`).  Per lane the operations and their order are those of dense<>: R2 for layers of
+// two or more units (first product rounded, then FMAs), R3 for the single output unit (products rounded one by one,
+// unfused adds from +0: each add is fma(1, product, acc) with the run-time 1 so that ptxas cannot contract it with its
+// multiply.  The first one may NOT be shortened to fma(x, W, +0): a product that flushes to -0 must still add up to +0,
+// as the reference's goldens have it).  Every instruction is packed: no scalar FADD between packed FMAs, which cost
+// two FMA-pipe cycles each (profiles/r02_issue_mix.txt).
+template <class S, int L, bool ANYZERO>
+SRNN_DEV void mlp_forward_pair(const float *w, const f32x2_t *x, float &y0, float &y1, float one) {
+    constexpr int IN = S::in(L), OUT = S::out(L);
+    const float *W = w + S::off(L);
+    f32x2_t h[OUT];
+    if constexpr (OUT >= 2) {
+#pragma unroll
+        for (int j = 0; j < OUT; ++j) {
+            f32x2_t acc = mul2(x[0], pack2(W[j], W[j]));
+#pragma unroll
+            for (int k = 1; k < IN; ++k) acc = fma2(x[k], pack2(W[k * OUT + j], W[k * OUT + j]), acc);
+            h[j] = acc;
+        }
+    } else {
+        // ANYZERO: (+0 + p0) spelled fma(x0, W0, +0) -- one instruction less; the same number, except that a product
+        // flushed to -0 stays -0 where the reference gets +0 (see ww_apply for when that is allowed).
+        f32x2_t acc = ANYZERO ? fma2(x[0], pack2(W[0], W[0]), pack2(0.0f, 0.0f))
+                              : fma2(pack2(one, one), mul2(x[0], pack2(W[0], W[0])), pack2(0.0f, 0.0f));
+#pragma unroll
+        for (int k = 1; k < IN; ++k) acc = fma2(pack2(one, one), mul2(x[k], pack2(W[k], W[k])), acc);
+        h[0] = acc;
+    }
+    if constexpr (L == S::NL - 1) unpack2(h[0], y0, y1);
+    else mlp_forward_pair<S, L + 1, ANYZERO>(w, h, y0, y1, one);
+}
+#endif
+
+// ANYZERO = true is the form for the INNER steps of a fixed-length self-application chain whose intermediate states
+// nobody sees: its results equal the exact form's in every bit except that a zero may carry either sign.  The sign of a
+// zero never reaches a non-zero value, a NaN or the zero / non-zero pattern of anything computed from it (a zero times
+// anything finite is a zero, a zero plus x is x, 0 * Inf is NaN whatever the sign), and the exact form's output sum
+// starts from +0, so its own zeros do not depend on the signs of the zeros it was given.  Hence: any number of ANYZERO
+// applications followed by ONE exact application is bit-identical to the all-exact chain (tests/test_gpu_parity.py::
+// test_self_apply_fixed_bitwise, test_self_apply_fixed_zero_signs, the reference's golden trajectories).
+template <class S, bool ANYZERO = false>
 SRNN_DEV void ww_apply(const float *op, const float *in, float *out, float one) {
+#if SRNN_PACKED_F32X2
+    if constexpr (S::OUTW == 1) {
+        // two weight points per instruction; a position code of exactly 1 multiplies by the run-time 1 (see opaque_one:
+        // with the literal, points with layer code 1 lost a rounding -- caught by the parity tests)
+        static_for<0, S::NW / 2>([&](auto M) {
+            constexpr int k = 2 * decltype(M)::value;
+            auto code_pair = [&](float c0, float c1) { return pack2(c0 == 1.0f ? one : c0, c1 == 1.0f ? one : c1); };
+            const f32x2_t x[4] = {pack2(in[k], in[k + 1]), code_pair(S::codeL(k), S::codeL(k + 1)),
+                                  code_pair(S::codeR(k), S::codeR(k + 1)), code_pair(S::codeC(k), S::codeC(k + 1))};
+            mlp_forward_pair<S, 0, ANYZERO>(op, x, out[k], out[k + 1], one);
+        });
+        if constexpr (S::NW % 2 == 1) {
+            constexpr int k = S::NW - 1;
+            const float x[4] = {in[k], S::codeL(k), S::codeR(k), S::codeC(k)};
+            mlp_forward<S>(op, x, &out[k]);
+        }
+        return;
+    }
+#endif
     static_for<0, S::NW>([&](auto K) {
         constexpr int k = decltype(K)::value;
 #if SRNN_PACKED_F32X2
@@ -275,37 +336,64 @@ SRNN_DEV void rnn_forward_seq(const float *op, const float *seq, float *out, flo
     });
 }
 // `one` = opaque_one(), fetched once per thread by the caller (hoisted out of the step loops)
-template <class S>
+template <class S, bool ANYZERO = false>
 SRNN_DEV void net_apply(const float *op, const float *in, float *out, float one) {
-    if constexpr (S::KIND == SRNN_KIND_WW) ww_apply<S>(op, in, out, one);
+    if constexpr (S::KIND == SRNN_KIND_WW) ww_apply<S, ANYZERO>(op, in, out, one);
     else if constexpr (S::KIND == SRNN_KIND_AGG) agg_apply<S>(op, in, out);
     else rnn_forward_seq<S, false>(op, in, out, nullptr);
 }
 
 // ------------------------------------------------------------------------------------------------ predicates
-// are_weights_diverged, code/network.py:43-52
-template <int N>
-SRNN_DEV bool is_diverged(const float *w) {
-    bool d = false;
-#pragma unroll
-    for (int k = 0; k < N; ++k) d |= !(fabsf(w[k]) <= 3.402823466e+38f);
+// All three predicates are reductions to ONE number and one compare (7 three-input FMNMX for 14 weights instead of 14
+// compares and 7 predicate merges each -- ALU instructions next to packed FMAs are not free, profiles/r02_issue_mix.txt):
+//   m = NaN-propagating max_k |w_k|:   diverged <=> !(m <= FLT_MAX)   (m is NaN or Inf iff some weight is)
+//                                      zero     <=> m <= eps_le       (NaN compares false, like every element would)
+//   md = NaN-ignoring max_k |nw_k - w_k|:  every !(|d_k| >= eps) holds <=> !(md >= eps)  (a NaN d_k passes its own test
+//                                      and is skipped by fmaxf; all NaN gives NaN, which passes too)
+// -- the same booleans as the element-wise forms for every input, NaN and Inf included.
+SRNN_DEV float max_nan(float a, float b) {
+    float d;
+    asm("max.NaN.ftz.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
     return d;
 }
+template <int N>
+SRNN_DEV float max_abs_nan(const float *w) {
+    float m = fabsf(w[0]);
+#pragma unroll
+    for (int k = 1; k < N; ++k) m = max_nan(m, fabsf(w[k]));
+    return m;
+}
+template <int N>
+SRNN_DEV float max_abs_diff(const float *nw, const float *w) {
+    float d[N];
+#if SRNN_PACKED_F32X2
+#pragma unroll
+    for (int k = 0; k + 1 < N; k += 2) {
+        f32x2_t r;
+        asm("sub.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pack2(nw[k], nw[k + 1])), "l"(pack2(w[k], w[k + 1])));
+        unpack2(r, d[k], d[k + 1]);
+    }
+    if constexpr (N % 2 == 1) d[N - 1] = __fsub_rn(nw[N - 1], w[N - 1]);
+#else
+#pragma unroll
+    for (int k = 0; k < N; ++k) d[k] = __fsub_rn(nw[k], w[k]);
+#endif
+    float m = fabsf(d[0]);
+#pragma unroll
+    for (int k = 1; k < N; ++k) m = fmaxf(m, fabsf(d[k]));
+    return m;
+}
+SRNN_DEV bool diverged_from_max(float m) { return !(m <= 3.402823466e+38f); }
+// are_weights_diverged, code/network.py:43-52
+template <int N>
+SRNN_DEV bool is_diverged(const float *w) { return diverged_from_max(max_abs_nan<N>(w)); }
 // is_zero, code/network.py:136-138: all -eps <= w <= eps  (eps_le = largest f32 <= eps)
 template <int N>
-SRNN_DEV bool is_zero(const float *w, float eps_le) {
-    bool z = true;
-#pragma unroll
-    for (int k = 0; k < N; ++k) z &= (fabsf(w[k]) <= eps_le);
-    return z;
-}
+SRNN_DEV bool is_zero(const float *w, float eps_le) { return max_abs_nan<N>(w) <= eps_le; }
 // tail of is_fixpoint, code/network.py:149-157: nw = iterated application result (eps_ge = smallest f32 >= eps)
 template <int N>
 SRNN_DEV bool is_close(const float *nw, const float *w, float eps_ge) {
-    bool ok = !is_diverged<N>(nw);
-#pragma unroll
-    for (int k = 0; k < N; ++k) ok &= !(fabsf(__fsub_rn(nw[k], w[k])) >= eps_ge);
-    return ok;
+    return !is_diverged<N>(nw) && !(max_abs_diff<N>(nw, w) >= eps_ge);
 }
 // decision list of FixpointExperiment.count, code/experiment.py:79-91; nw = f_w(w) already known
 template <class S>

@@ -53,6 +53,32 @@ def test_self_apply_fixed_bitwise(eng, key):
         assert_same_weights(pop.numpy(), ref, "%r n=%d steps=%d" % (key, n, steps))
 
 
+@pytest.mark.parametrize("key", [k for k in SHAPES if k[0] == 0])
+def test_self_apply_fixed_zero_signs(eng, key):
+    """The fixed-length kernel runs its inner steps in a form that may leave zeros with either sign and only the last
+    step in the exact form (csrc/srnn_device.cuh, ww_apply ANYZERO).  Adversarial populations for exactly that: weights
+    so small that products and sums flush to zero (of both signs), explicit -0 / +0 entries, a few Inf / NaN rows --
+    every step count must equal the oracle's all-exact chain in every bit, signs of zeros included."""
+    dg, do = both(eng, key)
+    rng = np.random.default_rng(77)
+    n, nw = 6000, dg.n_weights
+    w = glorot_population(key, n, seed=78)
+    scale = np.float32(10.0) ** rng.integers(-24, 1, size=(n, 1)).astype(np.float32)   # 1e-24 .. 1: underflow within 1-3 steps
+    w = (w * scale).astype(np.float32)
+    w[rng.random((n, nw)) < 0.15] = np.float32(-0.0)
+    w[rng.random((n, nw)) < 0.10] = np.float32(0.0)
+    w[5, 3], w[6, 0], w[7, nw - 1] = np.inf, np.nan, -np.inf
+    saw_negative_zero = False
+    for steps in (1, 2, 3, 4, 5, 8, 33):
+        pop = eng.Population.from_numpy(dg, w)
+        pop.self_apply(steps)
+        ref = w.copy()
+        oracle.self_apply(do, ref, steps)
+        assert_same_weights(pop.numpy(), ref, "%r steps=%d" % (key, steps))
+        saw_negative_zero |= bool(((ref == 0) & np.signbit(ref)).any())
+    assert saw_negative_zero, "the case is meant to produce legitimate negative zeros as well"
+
+
 @pytest.mark.parametrize("key", BENCH_SHAPES)
 def test_self_apply_strided_records(eng, key):
     """ld > n_weights (padded records) takes the un-staged path."""
@@ -254,6 +280,11 @@ def test_kfv_bitwise_and_statistics(eng, golden_dir):
         hist = out["hist"].cpu().numpy()
         assert np.array_equal(hist[0], np.bincount(ys, minlength=101))
         assert np.array_equal(hist[1], np.bincount(zs, minlength=101))
+        # without the weights the kernel may leave zeros of either sign inside its loop: the counts must not notice
+        lean = eng.kfv(dg, base, n, scale, level, 100, 1e-4, seed=99, slot0=5)
+        assert lean["w"] is None
+        assert np.array_equal(lean["ys"].cpu().numpy(), ys) and np.array_equal(lean["zs"].cpu().numpy(), zs)
+        assert np.array_equal(lean["hist"].cpu().numpy(), hist)
         ry = g["ys"][level * 100:(level + 1) * 100]
         assert abs(ys.mean() - ry.mean()) < 4 * max(ry.std(), 0.3) / 10 + 0.1
         scale /= 10.0
