@@ -1,3 +1,3 @@
-timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -6
-bash tools/profile_round.sh r02b 2>&1 | tail -5
-ls gpurun_out | tail -12
+export SRNN_LIB=$PWD/build/variants/dev_skip.so
+python bench.py --no-legs 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('headline %.4e  e2e %.3e  frac %.3f' % (d['value'], d['e2e']['value'], d['roofline']['frac']))"
+timeout 900 python -m pytest tests/test_gpu_parity.py -q -m gpu -k "self_apply or golden or nan_inf" 2>&1 | tail -5
