@@ -1,2 +1,6 @@
-timeout 900 python -m pytest tests/test_sharded_soup.py tests/test_gpu_facade.py -q -m gpu 2>&1 | tail -5 > gpurun_out/r02_pytest_2gpu.log; cat gpurun_out/r02_pytest_2gpu.log
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 > gpurun_out/r02_bench_2gpu.json 2> gpurun_out/r02_bench_2gpu.err; echo bench rc=$?; tail -c 400 gpurun_out/r02_bench_2gpu.err
+python tools/prof_mixed.py
+python tools/prof_soup.py 10000000 20 0
+python tools/prof_soup.py 10000000 20 1
+PROF_KIND=1 python tools/prof_soup.py 3333328 20 0
+PROF_KIND=2 python tools/prof_soup.py 3333328 20 0
+timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_sharded_soup.py tests/test_gpu_facade.py -q -m gpu -k "soup or evolve" 2>&1 | tail -5
