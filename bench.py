@@ -12,7 +12,8 @@ L2), all resident in HBM before the timed region starts.
 
   value    whole-job self-applications/s, device-timed (CUDA events), max over ranks
   e2e      same metric through the host API with HOST inputs: pinned-host -> device copy of the step's
-           14-float records, kernel + fused classification, class counters back to the host, double-buffered
+           14-float records, kernel + fused classification, final weights and class counters back to the host,
+           three arenas in flight
   roofline the kernel against the FP32 issue roofline (bound "fp32"): achieved = 392 algorithmic FLOP per
            self-application / kernel time; peak = an FFMA-only probe kernel measured live on the same GPU
   cpu_baseline  the oracle's SIMD/OpenMP WW(2,2) path on the box's host cores, on a bounded sample
