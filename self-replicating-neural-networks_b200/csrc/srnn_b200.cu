@@ -1299,6 +1299,28 @@ __device__ __forceinline__ void soup_tile_generation(int64_t tile_idx, const Sha
         if (i < n) {
             float cur[NW];
             tile_get<NW>(tile, v, cur);
+            if constexpr (!DEFER && PPT == 1 && S::KIND == SRNN_KIND_WW && S::NW <= 16) {
+                // the one-particle-per-thread build only serves small TRAINING soups: the self-training kernel's epoch
+                // (samples unrolled, order in one register, one Philox block per EPB epochs) is worth its size here --
+                // 30 epochs per generation 19 % faster; inside the large-soup builds it cost 4-5 %
+                // (profiles/r02_soup_train_unrolled_ab.txt)
+                U4 blk;
+                uint64_t blk_id = ~0ull;
+                for (int e = 0; e < tr; ++e) {
+#pragma unroll
+                    for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = cur[k];
+                    const bool last = e == tr - 1;   // only the last epoch's loss is reported
+                    if (ordered) {
+                        uint32_t rw[PermPlan<S::NS>::W];
+                        perm_words<S::NS>(seed, (uint64_t)(slot0 + i), ep + (uint64_t)(sev + e), rw, blk, blk_id);
+                        const uint64_t order = perm_nibbles<S::NS>(rw);
+                        if (last) ls[r] = ww_epoch_unrolled<S, true, true>(cur, sc.tgt, sc.stride, sc.codes, order, p.lr, sc.one);
+                        else ww_epoch_unrolled<S, true, false>(cur, sc.tgt, sc.stride, sc.codes, order, p.lr, sc.one);
+                    } else {
+                        ls[r] = ww_epoch_unrolled<S, false, true>(cur, sc.tgt, sc.stride, sc.codes, 0, p.lr, sc.one);
+                    }
+                }
+            } else
             for (int e = 0; e < (DEFER ? 0 : tr); ++e) {   // (the deferring build is only launched for generations without training)
 #pragma unroll
                 for (int k = 0; k < NW; ++k) sc.tgt[k * sc.stride] = cur[k];

@@ -470,6 +470,42 @@ def test_soup_deferred_learners(eng, key):
         snap, ref = out, rout
 
 
+@pytest.mark.parametrize("key", BENCH_SHAPES)
+@pytest.mark.parametrize("perm_mode", [2, 0])
+def test_soup_run_small_training_soup(eng, key, perm_mode):
+    """Small training soups (one wave of CTAs) run one particle per thread, weightwise ones with the self-training kernel's
+    unrolled epoch: several epochs per generation (loss-less epochs + the reported last one), Philox and fixed sample
+    order, through the chained run -- against the oracle's generations."""
+    import torch
+    dg, do = both(eng, key)
+    n = 3000
+    kw = dict(attacking_rate=0.3, learn_from_rate=0.2, train=4, learn_from_severity=2, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=perm_mode)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population(key, n, seed=61)
+    ref = w.copy()
+    a = torch.from_numpy(w).cuda()
+    b = torch.zeros_like(a)
+    scratch = torch.zeros(eng.soup_scratch_len(n, n), dtype=torch.int32, device="cuda")
+    gens = 3
+    for gen in range(1, gens + 1):
+        rout = np.zeros_like(ref)
+        oracle.soup_sync(do, po, ref, n, rout, 0, n, 17, gen)
+        ref = rout
+    eng.soup_sync_run(dg, pg, a, b, 17, 1, gens, scratch)
+    assert_same_weights((b if gens % 2 else a).cpu().numpy(), ref, "%r perm_mode %d" % (key, perm_mode))
+    # one generation through the per-call entry, with the loss of the last epoch
+    out = torch.zeros_like(a)
+    loss = torch.zeros(n, dtype=torch.float64, device="cuda")
+    start = torch.from_numpy(w).cuda()
+    eng.soup_sync(dg, pg, start, n, out, 0, n, 17, 1, scratch, loss=loss)
+    rout = np.zeros_like(w)
+    _, rl, _ = oracle.soup_sync(do, po, w, n, rout, 0, n, 17, 1)
+    assert_same_weights(out.cpu().numpy(), rout)
+    gl = loss.cpu().numpy()
+    assert np.array_equal(np.isnan(gl), np.isnan(rl)) and np.array_equal(gl[~np.isnan(gl)], rl[~np.isnan(rl)])
+
+
 @pytest.mark.parametrize("key", SHAPES)
 @pytest.mark.parametrize("n", [1, 255, 256, 257, 1000])
 def test_soup_sync_every_fast_shape_and_ragged_tiles(eng, key, n):
