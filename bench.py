@@ -452,8 +452,9 @@ def secondary_legs(eng, torch, dist, rank, world, dev, probe):
         from oracle import numpy_twin
         fac = facade_bench.run()
         fac["numpy_twin_1core_self_applications_per_s"] = numpy_twin.self_applications_per_second()
-        fac["note"] = ("per-object path: launch- and host-sync-bound by construction (one kernel + one device read per "
-                       "method call); populations go through Soup / srnn_engine")
+        fac["note"] = ("per-object path: host-bound by construction (self_attack() calls of a net are deferred into one "
+                       "launch, then one launch + one device read per net for count); populations go through Soup / "
+                       "srnn_engine")
         out["facade"] = fac
     except Exception as exc:        # the facade leg must never take the headline down
         out["facade"] = {"error": repr(exc)}

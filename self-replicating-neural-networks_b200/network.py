@@ -169,6 +169,26 @@ class NeuralNetwork(PrintingObject):  # noqa: F405
         self.states = []
         self._version = 0
         self._flag_cache = None
+        self._pending = 0      # self_attack() steps not yet run on the device (see _pop)
+        self._row = None
+
+    # ---- the arena row behind this net.  self_attack() of a fused net is DEFERRED: the calls only count up, and the next
+    #      access to the row -- any read, write, attack, predicate, training, soup adoption: everything goes through this
+    #      property -- runs them as ONE srnn_self_apply launch (n launches of one step and one launch of n steps give the
+    #      same bits).  applying-fixpoints.py's `for _ in range(100): net.self_attack()` is one launch instead of 100.
+    @property
+    def _pop(self):
+        if self._pending:
+            steps, self._pending = self._pending, 0
+            self._row.self_apply(steps)
+        return self._row
+
+    @_pop.setter
+    def _pop(self, view):
+        if self.__dict__.get("_pending") and self.__dict__.get("_row") is not None:
+            steps, self._pending = self._pending, 0
+            self._row.self_apply(steps)     # the old row keeps the state it was owed
+        self._row = view
 
     def _bind(self, kind, width, depth, aggregates=0):
         self._desc = _eng.make_desc(kind, width, depth, aggregates)
@@ -262,7 +282,7 @@ class NeuralNetwork(PrintingObject):  # noqa: F405
 
     def self_attack(self, iterations=1):
         if self._fused():
-            self._pop.self_apply(int(iterations))
+            self._pending += int(iterations)
             self._touch()
         else:
             for _ in range(iterations):
@@ -326,10 +346,11 @@ class NeuralNetwork(PrintingObject):  # noqa: F405
         twin = self.__class__.__new__(self.__class__)
         memo[id(self)] = twin
         for k, v in self.__dict__.items():
-            if k in ("_pop", "_release", "model", "_flag_cache"):
+            if k in ("_row", "_pending", "_release", "model", "_flag_cache"):
                 continue
             twin.__dict__[k] = copy.deepcopy(v, memo)  # noqa: F405
         heap = _heap(self._desc)
+        twin._pending, twin._row = 0, None
         twin._pop, token = heap.take()
         twin._release = weakref.finalize(twin, heap.give_back, token)
         twin._pop.w.copy_(self._pop.w)
