@@ -44,6 +44,10 @@ constexpr int64_t SOUP_MULTIPASS_MIN = INT64_MAX;
 constexpr int64_t SOUP_CHAIN_MAX = SRNN_SOUP_CHAIN_MAX;
 // largest unsharded soup the opt-in persistent cooperative variant of srnn_soup_sync_run accepts
 constexpr int64_t SOUP_PERSISTENT_MAX = 1 << 20;
+#ifndef SRNN_EXACT_SPLIT_MIN
+#define SRNN_EXACT_SPLIT_MIN (1 << 22)   // measured: 10 M particles 1.444 -> 1.392 ms per generation, 1.1 M 0.226 -> 0.238 ms
+#endif
+constexpr int64_t SOUP_EXACT_SPLIT_MIN = SRNN_EXACT_SPLIT_MIN;
 
 // ------------------------------------------------------------------------------------------------ errors
 static thread_local char g_err[512] = "";
@@ -935,13 +939,35 @@ __device__ __forceinline__ void block_push(int32_t *counter, int32_t *list, int3
     if (pred) list[*s_base + wbase + __popc(m & ((1u << lane) - 1u))] = value;
 }
 
+// P1 of an exact-order generation for particle i: its pairings (given or drawn) and its place in its victim's / teacher's lists
+__device__ __forceinline__ void exact_prepare_one(const SoupP &p, uint64_t seed, uint64_t gen, int64_t n,
+                                                  const int64_t *__restrict__ att_in, const int64_t *__restrict__ lrn_in,
+                                                  const ExactBufs &b, int64_t i) {
+    int64_t a, l;
+    if (att_in) { a = att_in[i]; l = lrn_in[i]; }
+    else soup_draw(p, seed, (uint64_t)i, gen, n, &a, &l);
+    b.att32[i] = (int32_t)a;
+    b.lrn32[i] = (int32_t)l;
+    if (a >= 0) b.nextA[i] = atomicExch(&b.headA[a], (int32_t)i);
+    if (l >= 0) b.nextL[i] = atomicExch(&b.headL[l], (int32_t)i);
+}
+// The same as an ordinary launch at full occupancy (large soups: the cooperative kernel holds 3 CTAs per SM, and this
+// atomics-bound pass takes 169 us of a 10 M-particle generation in there); heads / stamps / counters are reset by memsets.
+__global__ void __launch_bounds__(BS) soup_exact_prepare_kernel(SoupP p, uint64_t seed, uint64_t gen, int64_t n,
+                                                                const int64_t *__restrict__ att_in,
+                                                                const int64_t *__restrict__ lrn_in, ExactBufs b) {
+    const int64_t i = (int64_t)blockIdx.x * BS + threadIdx.x;
+    if (i < n) exact_prepare_one(p, seed, gen, n, att_in, lrn_in, b, i);
+}
+
 template <class S>
 __global__ void __launch_bounds__(BS, SRNN_EXACT_MINB) soup_exact_coop_kernel(float *w, int64_t ld, int64_t n, SoupP p, uint64_t seed,
                                                              uint64_t gen0, int n_gens, Limits lim,
                                                              const int64_t *__restrict__ att_in,
                                                              const int64_t *__restrict__ lrn_in, ExactBufs b,
                                                              uint8_t *action, double *loss, uint8_t *dead_out,
-                                                             int32_t *rounds_out) {
+                                                             int32_t *rounds_out, int prepared) {
+    // prepared != 0: P0 and P1 of the (single) generation were done by memsets + soup_exact_prepare_kernel
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ __align__(16) float tile[BS * S::NW];
     __shared__ int s_cnt, s_base;
@@ -963,22 +989,16 @@ __global__ void __launch_bounds__(BS, SRNN_EXACT_MINB) soup_exact_coop_kernel(fl
         tl = 0;
 #endif
         TSTAMP();
-        // ---- P0
-        for (int64_t i = gtid; i < n; i += gsize) { b.headA[i] = -1; b.headL[i] = -1; b.stamp[i] = 0; }
-        if (gtid < 5 && gtid != 3) b.cnt[gtid] = 0;
-        grid_barrier(b.barrier, target);
-        TSTAMP();
-        // ---- P1
-        for (int64_t i = gtid; i < n; i += gsize) {
-            int64_t a, l;
-            if (att_in) { a = att_in[i]; l = lrn_in[i]; }
-            else soup_draw(p, seed, (uint64_t)i, gen, n, &a, &l);
-            b.att32[i] = (int32_t)a;
-            b.lrn32[i] = (int32_t)l;
-            if (a >= 0) b.nextA[i] = atomicExch(&b.headA[a], (int32_t)i);
-            if (l >= 0) b.nextL[i] = atomicExch(&b.headL[l], (int32_t)i);
+        if (!prepared) {
+            // ---- P0
+            for (int64_t i = gtid; i < n; i += gsize) { b.headA[i] = -1; b.headL[i] = -1; b.stamp[i] = 0; }
+            if (gtid < 5 && gtid != 3) b.cnt[gtid] = 0;
+            grid_barrier(b.barrier, target);
+            TSTAMP();
+            // ---- P1
+            for (int64_t i = gtid; i < n; i += gsize) exact_prepare_one(p, seed, gen, n, att_in, lrn_in, b, i);
+            grid_barrier(b.barrier, target);
         }
-        grid_barrier(b.barrier, target);
         TSTAMP();
         // ---- P2a: streaming pass.  A particle nobody touches and that touches nobody (about 2/3 of a soup at rates 0.1 / 0.1)
         //      has no predecessor: its turn runs here, with coalesced traffic only.  The others are compacted.
@@ -2684,8 +2704,10 @@ static int soup_exact_launch(const srnn_net_desc *d, const srnn_soup_params *p, 
     b.cnt = b.wl[1] + n + (n + 1) / 2;
     b.barrier = reinterpret_cast<unsigned *>(b.cnt + 6);
     if (rounds_last) *rounds_last = b.cnt + 3;
-    cudaError_t ce = cudaMemsetAsync(b.barrier, 0, sizeof(unsigned), st);
-    if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    // Every generation of the call inside ONE cooperative launch -- except for very large soups (2^22 particles and more),
+    // where the list pass is worth an ordinary launch of its own: per generation memsets + prepare + cooperative kernel.
+    const bool split = n >= SOUP_EXACT_SPLIT_MIN;
+    cudaError_t ce = cudaSuccess;
 #define BODY(S)                                                                                              \
     SRNN_CHECK_ARENA(w, ld, S)                                                                               \
     const size_t sm = sgd_smem_bytes<S>(BS);                                                                 \
@@ -2697,9 +2719,25 @@ static int soup_exact_launch(const srnn_net_desc *d, const srnn_soup_params *p, 
     ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, soup_exact_coop_kernel<S>, BS, sm);          \
     if (ce != cudaSuccess || per_sm < 1) return fail(SRNN_ERR_CUDA, "occupancy query: %s", cudaGetErrorString(ce)); \
     const unsigned grid = (unsigned)std::min<int64_t>((n + BS - 1) / BS, (int64_t)per_sm * sms);              \
-    void *args[] = {&w, &ld, &n, &q, &seed, &gen0, &n_gens, &lim, &att, &lrn, &b, &action, &loss, &dead, &rounds_dev}; \
-    ce = cudaLaunchCooperativeKernel((void *)soup_exact_coop_kernel<S>, dim3(grid), dim3(BS), args, sm, st);  \
-    if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cooperative launch: %s", cudaGetErrorString(ce));
+    for (int32_t g = 0; g < (split ? n_gens : 1); ++g) {                                                     \
+        uint64_t gen_g = gen0 + (uint64_t)g;                                                                 \
+        int32_t gens_g = split ? 1 : n_gens, prepared = split ? 1 : 0;                                       \
+        int32_t *rounds_g = rounds_dev ? rounds_dev + g : nullptr;                                           \
+        ce = cudaMemsetAsync(b.barrier, 0, sizeof(unsigned), st);                                            \
+        if (split) {                                                                                         \
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(b.headA, 0xFF, sizeof(int32_t) * (size_t)n, st);     \
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(b.headL, 0xFF, sizeof(int32_t) * (size_t)n, st);     \
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(b.stamp, 0, sizeof(uint16_t) * (size_t)n, st);       \
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(b.cnt, 0, sizeof(int32_t) * 6, st);                  \
+            if (ce == cudaSuccess)                                                                           \
+                soup_exact_prepare_kernel<<<grid_for(n), BS, 0, st>>>(q, seed, gen_g, n, att, lrn, b);       \
+        }                                                                                                    \
+        if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));    \
+        void *args[] = {&w, &ld, &n, &q, &seed, &gen_g, &gens_g, &lim, &att, &lrn, &b, &action, &loss, &dead, &rounds_g, \
+                        &prepared};                                                                          \
+        ce = cudaLaunchCooperativeKernel((void *)soup_exact_coop_kernel<S>, dim3(grid), dim3(BS), args, sm, st); \
+        if (ce != cudaSuccess) return fail(SRNN_ERR_CUDA, "cooperative launch: %s", cudaGetErrorString(ce)); \
+    }
     SRNN_DISPATCH(d)
 #undef BODY
     return check_launch("srnn_soup_exact");

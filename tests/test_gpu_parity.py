@@ -845,6 +845,39 @@ def test_soup_exact_order_wavefront(eng, key):
         assert np.array_equal(np.isnan(gl), np.isnan(rl)) and np.array_equal(gl[~np.isnan(gl)], rl[~np.isnan(rl)])
 
 
+def test_soup_exact_order_large_split_launches(eng):
+    """From 2^22 particles on an exact-order generation is memsets + an ordinary list-building launch + the cooperative
+    kernel (per generation) instead of one cooperative launch for everything: two generations in one srnn_soup_exact_run
+    call and one with host-supplied pairings through srnn_soup_exact, against the oracle's sequential sweep."""
+    import torch
+    dg, do = both(eng, (0, 2, 2, 0))
+    n = (1 << 22) + 333
+    kw = dict(attacking_rate=0.15, learn_from_rate=0.1, train=0, learn_from_severity=1, remove_divergent=True,
+              remove_zero=True, epsilon=1e-4, perm_mode=2)
+    pg, po = eng.make_soup_params(**kw), oracle.soup_params(**kw)
+    w = glorot_population((0, 2, 2, 0), n, seed=62)
+    arena = torch.from_numpy(w).cuda()
+    ref = w.copy()
+    scratch = torch.full((eng.soup_exact_scratch_len(n),), 0x3C3C3C3C, dtype=torch.int32, device="cuda")
+    action = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    rounds = torch.zeros(2, dtype=torch.int32, device="cuda")
+    eng.soup_exact_run(dg, pg, arena, 41, 1, 2, scratch, action=action, rounds=rounds)
+    for gen in (1, 2):
+        att, lrn = oracle.soup_draw(po, 41, gen, n)
+        ra, _ = oracle.soup_ordered(do, po, ref, att, lrn, seed=41, gen=gen)
+    assert_same_weights(arena.cpu().numpy(), ref, "two generations in one call")
+    assert np.array_equal(action.cpu().numpy(), ra) and (rounds.cpu().numpy() >= 3).all()
+    rng = np.random.default_rng(5)
+    att = np.where(rng.random(n) < 0.15, rng.integers(0, n, n), -1)
+    lrn = np.where(rng.random(n) < 0.1, rng.integers(0, n, n), -1)
+    r3 = eng.soup_exact(dg, pg, arena, 41, 3, scratch, att=torch.from_numpy(att).cuda(), lrn=torch.from_numpy(lrn).cuda(),
+                        action=action)
+    ra, _ = oracle.soup_ordered(do, po, ref, att, lrn, seed=41, gen=3)
+    assert r3 >= 3
+    assert_same_weights(arena.cpu().numpy(), ref, "host-supplied pairings")
+    assert np.array_equal(action.cpu().numpy(), ra)
+
+
 def test_population_soup_exact_mode(eng):
     import soup as soup_mod
     n = 6000
