@@ -245,6 +245,21 @@ int srnn_assign_uids(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *
 int srnn_assign_uids_static(const uint8_t *dead, int64_t n, int64_t uid_base, int64_t *uid, int64_t *n_dead_out,
                             void *stream);
 
+/* Communicator family for hosts without torch.distributed: the all-gather of the record arenas that the
+ * `allgather` exchange of a sharded soup needs (soup.py PopulationSoup does the same through torch.distributed; the
+ * peer-memory exchanges srnn_soup_sync_peers / srnn_soup_chain_peers need no communicator at all).  NCCL is looked up at
+ * run time (the libnccl.so.2 already loaded in the process, else the system's); without it the calls return
+ * SRNN_ERR_CUDA with a message.  One communicator per process and device:
+ *   rank 0: srnn_comm_unique_id(id)  ->  the host broadcasts the 128 bytes by its own means  ->
+ *   every rank, its GPU current: srnn_comm_init(id, rank, world, &comm)   (collective)
+ *   srnn_comm_allgather(comm, send, recv, count, stream): recv[r * count .. (r + 1) * count) = rank r's send[0 .. count),
+ *   floats, asynchronous on `stream`;  srnn_comm_destroy(comm). */
+#define SRNN_COMM_ID_BYTES 128
+int srnn_comm_unique_id(uint8_t *id_out);
+int srnn_comm_init(const uint8_t *id, int32_t rank, int32_t world, void **comm_out);
+int srnn_comm_allgather(void *comm, const float *send, float *recv, int64_t count, void *stream);
+int srnn_comm_destroy(void *comm);
+
 /* FP32 issue-rate probe: an FFMA-only kernel (independent chains, operands in registers) used as the
  * measured roofline denominator for the register-resident kernels (MEASURED_PEAKS.json has no FP32 entry).
  * Runs |iters| x 64 FMA per thread over grid x block threads; out = float[grid*block] sink.  iters > 0: three-register

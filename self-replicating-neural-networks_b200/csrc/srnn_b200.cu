@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <cstring>
 #include <mutex>
+#include <dlfcn.h>
 
 #include "../../include/srnn_b200.h"
 #include "srnn_device.cuh"
@@ -2851,6 +2852,89 @@ int srnn_soup_sync_run(const srnn_net_desc *d, const srnn_soup_params *p, float 
                                 stream);
         if (rc) return rc;
     }
+    return SRNN_OK;
+}
+
+// ---------------------------------------------------------------- communicator family (NCCL resolved at run time)
+extern "C++" {
+namespace {
+struct NcclId { char internal[SRNN_COMM_ID_BYTES]; };
+struct NcclApi {
+    int (*get_unique_id)(NcclId *) = nullptr;
+    int (*comm_init_rank)(void **, int, NcclId, int) = nullptr;
+    int (*all_gather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+    int (*comm_destroy)(void *) = nullptr;
+    const char *(*error_string)(int) = nullptr;
+    bool ok = false;
+};
+const NcclApi &nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);     // the copy already in the process (e.g. torch's)
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) return;
+        api.get_unique_id = reinterpret_cast<int (*)(NcclId *)>(dlsym(h, "ncclGetUniqueId"));
+        api.comm_init_rank = reinterpret_cast<int (*)(void **, int, NcclId, int)>(dlsym(h, "ncclCommInitRank"));
+        api.all_gather = reinterpret_cast<int (*)(const void *, void *, size_t, int, void *, cudaStream_t)>(
+            dlsym(h, "ncclAllGather"));
+        api.comm_destroy = reinterpret_cast<int (*)(void *)>(dlsym(h, "ncclCommDestroy"));
+        api.error_string = reinterpret_cast<const char *(*)(int)>(dlsym(h, "ncclGetErrorString"));
+        api.ok = api.get_unique_id && api.comm_init_rank && api.all_gather && api.comm_destroy && api.error_string;
+    });
+    return api;
+}
+int nccl_fail(const NcclApi &api, const char *what, int rc) {
+    char msg[192];
+    snprintf(msg, sizeof msg, "%s: %s", what, api.error_string ? api.error_string(rc) : "NCCL error");
+    return fail(SRNN_ERR_CUDA, "%s", msg);
+}
+}  // namespace
+}  // extern "C++"
+
+int srnn_comm_unique_id(uint8_t *id_out) {
+    if (!id_out) return fail(SRNN_ERR_ARG, "id_out is NULL%s");
+    const NcclApi &api = nccl_api();
+    if (!api.ok) return fail(SRNN_ERR_CUDA, "libnccl.so.2 could not be loaded%s");
+    NcclId id;
+    const int rc = api.get_unique_id(&id);
+    if (rc) return nccl_fail(api, "ncclGetUniqueId", rc);
+    memcpy(id_out, id.internal, SRNN_COMM_ID_BYTES);
+    return SRNN_OK;
+}
+
+int srnn_comm_init(const uint8_t *id, int32_t rank, int32_t world, void **comm_out) {
+    if (!id || !comm_out) return fail(SRNN_ERR_ARG, "id or comm_out is NULL%s");
+    if (world < 1 || rank < 0 || rank >= world) return fail(SRNN_ERR_ARG, "need 0 <= rank < world%s");
+    const NcclApi &api = nccl_api();
+    if (!api.ok) return fail(SRNN_ERR_CUDA, "libnccl.so.2 could not be loaded%s");
+    NcclId nid;
+    memcpy(nid.internal, id, SRNN_COMM_ID_BYTES);
+    void *comm = nullptr;
+    const int rc = api.comm_init_rank(&comm, world, nid, rank);
+    if (rc) return nccl_fail(api, "ncclCommInitRank", rc);
+    *comm_out = comm;
+    return SRNN_OK;
+}
+
+int srnn_comm_allgather(void *comm, const float *send, float *recv, int64_t count, void *stream) {
+    if (!comm || !send || !recv) return fail(SRNN_ERR_ARG, "comm, send or recv is NULL%s");
+    if (count < 0) return fail(SRNN_ERR_ARG, "count < 0%s");
+    if (count == 0) return SRNN_OK;
+    const NcclApi &api = nccl_api();
+    if (!api.ok) return fail(SRNN_ERR_CUDA, "libnccl.so.2 could not be loaded%s");
+    const int rc = api.all_gather(send, recv, (size_t)count, 7 /* ncclFloat32 */, comm, (cudaStream_t)stream);
+    if (rc) return nccl_fail(api, "ncclAllGather", rc);
+    return SRNN_OK;
+}
+
+int srnn_comm_destroy(void *comm) {
+    if (!comm) return SRNN_OK;
+    const NcclApi &api = nccl_api();
+    if (!api.ok) return fail(SRNN_ERR_CUDA, "libnccl.so.2 could not be loaded%s");
+    const int rc = api.comm_destroy(comm);
+    if (rc) return nccl_fail(api, "ncclCommDestroy", rc);
     return SRNN_OK;
 }
 

@@ -28,7 +28,8 @@ FLAG_DIVERGED, FLAG_ZERO, FLAG_FIX1, FLAG_FIX2 = 1, 2, 4, 8
 # every symbol include/srnn_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("srnn_version", "srnn_last_error_string", "srnn_set_device", "srnn_desc_init", "srnn_shape_supported",
            "srnn_apply", "srnn_forward", "srnn_self_apply", "srnn_classify", "srnn_train", "srnn_init", "srnn_kfv",
-           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_exact_run", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_chain_peers", "srnn_soup_push_lists", "srnn_soup_sync_run", "srnn_soup_log_watched", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe")
+           "srnn_soup_ordered", "srnn_soup_exact", "srnn_soup_exact_run", "srnn_soup_sync", "srnn_soup_sync_peers", "srnn_soup_chain_peers", "srnn_soup_push_lists", "srnn_soup_sync_run", "srnn_soup_log_watched", "srnn_assign_uids", "srnn_assign_uids_static", "srnn_fp32_probe",
+           "srnn_comm_unique_id", "srnn_comm_init", "srnn_comm_allgather", "srnn_comm_destroy")
 UIDS_STATIC_MAX = 1 << 24
 
 
@@ -417,6 +418,34 @@ def kfv(desc, base, n, scale, level, max_steps, eps, seed, slot0=0, want_times=T
                         C.c_uint32(level), C.c_int32(max_steps), C.c_double(eps), C.c_uint64(seed), C.c_uint64(slot0),
                         _ptr(ys), _ptr(zs), _ptr(hist), _ptr(wout), C.c_int64(desc.n_weights), _stream()))
     return dict(ys=ys, zs=zs, hist=hist, w=wout)
+
+
+class Comm:
+    """The C ABI's communicator (srnn_comm_*): NCCL all-gather of record arenas for hosts that do not use
+    torch.distributed.  Rank 0 calls Comm.unique_id() and ships the 128 bytes to the other ranks by any means; every rank
+    then builds Comm(id, rank, world) with its GPU current (collective)."""
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_uint8 * 128)()
+        _chk(lib().srnn_comm_unique_id(buf))
+        return bytes(buf)
+
+    def __init__(self, uid, rank, world):
+        buf = (C.c_uint8 * 128).from_buffer_copy(uid)
+        self._h = C.c_void_p()
+        _chk(lib().srnn_comm_init(buf, C.c_int32(rank), C.c_int32(world), C.byref(self._h)))
+        self.rank, self.world = rank, world
+
+    def allgather(self, send, recv):
+        """recv[r * send.numel() ...] = rank r's send (float32 device tensors), asynchronous on the current stream."""
+        assert recv.numel() == self.world * send.numel()
+        _chk(lib().srnn_comm_allgather(self._h, _ptr(send), _ptr(recv), C.c_int64(send.numel()), _stream()))
+
+    def destroy(self):
+        if self._h:
+            _chk(lib().srnn_comm_destroy(self._h))
+            self._h = C.c_void_p()
 
 
 def fp32_probe(iters=4096, variant=0, blocks_per_sm=8, device=None):

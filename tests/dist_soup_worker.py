@@ -112,9 +112,21 @@ def main():
     uids = torch.zeros(ps.size, dtype=torch.int64, device=ps.w.device)
     dist.all_gather_into_tensor(full, ps.w.contiguous())
     dist.all_gather_into_tensor(uids, ps.uid)
+    comm_ok = -1
+    if args.backend == "nccl":
+        # the C ABI's own communicator (srnn_comm_*): same all-gather without torch.distributed on the data path
+        import srnn_engine as eng
+        box = [eng.Comm.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        comm = eng.Comm(box[0], rank, world)
+        again = torch.zeros_like(full)
+        comm.allgather(ps.w.contiguous(), again)
+        torch.cuda.synchronize()
+        comm_ok = int(torch.equal(again.view(torch.int32), full.view(torch.int32)))
+        comm.destroy()
     if rank == 0:
         np.savez(args.out, w=full.cpu().numpy(), uid=uids.cpu().numpy(), counts=np.array(list(counts.values())),
-                 next_uid=ps.next_uid, world=world, exchange=ps.exchange)
+                 next_uid=ps.next_uid, world=world, exchange=ps.exchange, comm_ok=comm_ok)
     dist.barrier()
     dist.destroy_process_group()
 

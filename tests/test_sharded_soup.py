@@ -81,6 +81,7 @@ def test_two_ranks_nccl_equals_one(kind, exchange, tmp_path):
     got = _run("nccl", 2, kind, 8192, 3, tmp_path, exchange)
     assert int(got["world"]) == 2 and str(got["exchange"]) == exchange
     _check(got, kind, 8192, 3)
+    assert int(got["comm_ok"]) == 1      # srnn_comm_allgather (the C ABI's own NCCL communicator) == torch's all-gather
 
 
 @pytest.mark.gpu
