@@ -353,14 +353,15 @@ __global__ void __launch_bounds__(BS) self_apply_fixed_kernel(float *__restrict_
     if (base + threadIdx.x < n) {
         const float one = opaque_one();
         // all applications but the last may leave zeros with either sign (ww_apply, ANYZERO): nobody sees those states,
-        // and the exact last application restores the reference's result bit for bit
+        // and -- for the shapes where that holds -- the exact last application restores the reference's result bit for bit
+        constexpr bool AZ = exact_step_ignores_zero_signs<S>();
         int s = 0;
         for (; s + 2 <= n_steps - 1; s += 2) {  // ping-pong: no register copies between steps
-            net_apply<S, true>(a, a, b, one);
-            net_apply<S, true>(b, b, a, one);
+            net_apply<S, AZ>(a, a, b, one);
+            net_apply<S, AZ>(b, b, a, one);
         }
         if (s < n_steps - 1) {
-            net_apply<S, true>(a, a, b, one);
+            net_apply<S, AZ>(a, a, b, one);
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) a[k] = b[k];
         }
@@ -393,12 +394,13 @@ __global__ void __launch_bounds__(BS) self_apply_general_kernel(float *__restric
         // and one more application afterwards for the classifier's fixpoint test
         const float one = opaque_one();
         int s = 0;
+        constexpr bool AZ = exact_step_ignores_zero_signs<S>();
         for (; s + 2 <= n_steps - 1; s += 2) {   // inner steps: zeros of either sign (ww_apply, ANYZERO); last step exact
-            net_apply<S, true>(cur, cur, nxt, one);
-            net_apply<S, true>(nxt, nxt, cur, one);
+            net_apply<S, AZ>(cur, cur, nxt, one);
+            net_apply<S, AZ>(nxt, nxt, cur, one);
         }
         if (s < n_steps - 1) {
-            net_apply<S, true>(cur, cur, nxt, one);
+            net_apply<S, AZ>(cur, cur, nxt, one);
 #pragma unroll
             for (int k = 0; k < S::NW; ++k) cur[k] = nxt[k];
         }

@@ -211,13 +211,20 @@ SRNN_DEV void mlp_forward_pair(const float *w, const f32x2_t *x, float &y0, floa
 }
 #endif
 
-// ANYZERO = true is the form for the INNER steps of a fixed-length self-application chain whose intermediate states
-// nobody sees: its results equal the exact form's in every bit except that a zero may carry either sign.  The sign of a
-// zero never reaches a non-zero value, a NaN or the zero / non-zero pattern of anything computed from it (a zero times
-// anything finite is a zero, a zero plus x is x, 0 * Inf is NaN whatever the sign), and the exact form's output sum
-// starts from +0, so its own zeros do not depend on the signs of the zeros it was given.  Hence: any number of ANYZERO
-// applications followed by ONE exact application is bit-identical to the all-exact chain (tests/test_gpu_parity.py::
-// test_self_apply_fixed_bitwise, test_self_apply_fixed_zero_signs, the reference's golden trajectories).
+// ANYZERO = true is the form for steps whose resulting zeros nobody sees with their sign: its results equal the exact
+// form's in every bit except that a zero may carry either sign.  (A) The sign of a zero never reaches a non-zero value,
+// a NaN or the zero / non-zero pattern of anything computed from it (a zero times anything finite is a zero, a zero plus
+// x is x, 0 * Inf is NaN whatever the sign) -- so tests that look at magnitudes only (the KFV loop) may use it freely.
+// (B) When the single output unit has at most TWO inputs, the exact form's own zeros do not depend on the signs of the
+// zeros it was given: out = (+0 + p0) + p1, and +0 + p0 is +0 or non-zero, never -0.  Hence, for such shapes
+// (exact_step_ignores_zero_signs), any number of ANYZERO applications followed by ONE exact application is
+// bit-identical to the all-exact chain -- the fixed-length kernels run their inner steps this way.  With three or more
+// inputs (B) fails: a partial sum can underflow to -0 and the next product may be a zero of either sign
+// (tests/test_oracle_zero_signs.py shows both; tests/test_gpu_parity.py::test_self_apply_fixed_zero_signs).
+template <class S>
+SRNN_HD bool exact_step_ignores_zero_signs() {
+    return S::KIND == SRNN_KIND_WW && S::in(S::NL - 1) <= 2;
+}
 template <class S, bool ANYZERO = false>
 SRNN_DEV void ww_apply(const float *op, const float *in, float *out, float one) {
 #if SRNN_PACKED_F32X2
