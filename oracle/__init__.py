@@ -113,6 +113,16 @@ def self_apply(d, w, n_steps, mode=RUN_FIXED, eps=1e-14, traj=False, n=None):
     return (steps, tr) if traj else steps
 
 
+def self_apply_short_form(d, w, n_steps, exact_last=True, n=None):
+    """Test infrastructure: n_steps self-applications with steps 1 .. n-1 in the CUDA kernels' short form (a product
+    flushed to -0 keeps its sign in the output sum) and the last one exact (exact_last=False: short form throughout)
+    -- tests/test_oracle_zero_signs.py."""
+    n = w.shape[0] if n is None else n
+    pw, ld = _f32(w)
+    _chk(lib().srnn_oracle_self_apply_short_form(C.byref(d), pw, ld, C.c_int64(n), C.c_int32(n_steps),
+                                                 C.c_int32(1 if exact_last else 0)))
+
+
 def classify(d, w, eps, with_fix_sec=True, n=None):
     n = w.shape[0] if n is None else n
     cls = np.zeros(n, np.uint8)

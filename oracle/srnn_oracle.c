@@ -95,6 +95,10 @@ int srnn_oracle_desc_init(srnn_net_desc *d) {
 }
 
 /* ------------------------------------------------------------------ dense (R2 / R3) */
+/* Test-only switch (srnn_oracle_self_apply_short_form): emulate the CUDA kernels' short form of the single-output layer,
+ * whose first add "+0 + p0" is spelled fma(x0, W0, +0) -- the same number, except that a product flushed to -0 stays -0
+ * (csrc/srnn_device.cuh, ww_apply ANYZERO).  Never set on the reference-restating paths. */
+static __thread int g_short_form = 0;
 static inline void dense(const float *x, const float *W, int in, int out, float *y) {
     if (out >= 2) {
         for (int j = 0; j < out; ++j) {
@@ -104,7 +108,9 @@ static inline void dense(const float *x, const float *W, int in, int out, float 
         }
     } else {
         float acc = 0.0f;
-        for (int k = 0; k < in; ++k) { float p = x[k] * W[k]; acc = acc + p; }
+        int k0 = 0;
+        if (g_short_form) { acc = fmaf(x[0], W[0], 0.0f); k0 = 1; }
+        for (int k = k0; k < in; ++k) { float p = x[k] * W[k]; acc = acc + p; }
         y[0] = acc;
     }
 }
@@ -321,6 +327,34 @@ int srnn_oracle_self_apply(const srnn_net_desc *d, float *w, int64_t ld, int64_t
             }
             store_net(w, ld, i, s.n_weights, cur);
             if (steps_out) steps_out[i] = it;
+        }
+        ftz_restore(csr);
+    }
+    return SRNN_OK;
+}
+
+/* Test infrastructure for the zero-sign lemma (tests/test_oracle_zero_signs.py): n_steps self-applications the way the
+ * fixed-length CUDA kernels run them -- steps 1 .. n_steps-1 in the short form (zeros of either sign), the last one exact
+ * (exact_last = 0: every step in the short form, to show that the short form alone does differ). */
+int srnn_oracle_self_apply_short_form(const srnn_net_desc *d, float *w, int64_t ld, int64_t n, int32_t n_steps,
+                                      int32_t exact_last) {
+    shape_t s;
+    int rc = make_shape(d, &s);
+    if (rc) return rc;
+#pragma omp parallel
+    {
+        unsigned csr = ftz_on();
+#pragma omp for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+            float cur[MAXW], nxt[MAXW];
+            load_net(w, ld, i, s.n_weights, cur);
+            for (int32_t it = 0; it < n_steps; ++it) {
+                g_short_form = !exact_last || it < n_steps - 1;
+                net_apply(&s, cur, cur, nxt);
+                memcpy(cur, nxt, sizeof(float) * s.n_weights);
+            }
+            g_short_form = 0;
+            store_net(w, ld, i, s.n_weights, cur);
         }
         ftz_restore(csr);
     }

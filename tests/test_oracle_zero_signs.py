@@ -50,3 +50,34 @@ def test_exact_step_and_the_signs_of_zeros(key):
     assert flipped > 1000
     if not two_inputs:
         assert sign_only_differences > 0, "the width-3 counterexamples to (B) should show up in this population"
+
+
+@pytest.mark.parametrize("key", [(0, 2, 2, 0), (0, 2, 3, 0), (0, 2, 1, 0), (0, 3, 2, 0)])
+def test_short_inner_steps_then_one_exact_step(key):
+    """The kernels' schedule itself, emulated on the CPU (oracle.self_apply_short_form): steps 1 .. n-1 with the output
+    sum's first add spelled fma(x0, W0, +0), step n exact.  Width-2 shapes: equal to n exact steps in every bit, on 300 000
+    adversarial nets and 2 .. 12 steps -- although the short form alone does leave zeros with the other sign (shown by
+    running it without the exact finish).  WW(3,2): the schedule is NOT admitted (exact_step_ignores_zero_signs); here it
+    only has to keep magnitudes."""
+    d = oracle.desc(*key)
+    rng = np.random.default_rng(21)
+    n, nw = 300000, d.n_weights
+    w = glorot_population(key, n, seed=22)
+    w = (w * (np.float32(10.0) ** rng.integers(-26, 1, size=(n, 1)).astype(np.float32))).astype(np.float32)
+    w[rng.random((n, nw)) < 0.1] = np.float32(-0.0)
+    w[rng.random((n, nw)) < 0.1] = np.float32(0.0)
+    w[5, 0], w[6, 1], w[7, nw - 1] = np.inf, np.nan, -np.inf
+    sign_differences_without_the_finish = 0
+    for steps in (2, 3, 5, 12):
+        exact, short, unfinished = w.copy(), w.copy(), w.copy()
+        oracle.self_apply(d, exact, steps)
+        oracle.self_apply_short_form(d, short, steps)
+        oracle.self_apply_short_form(d, unfinished, steps, exact_last=False)
+        ok = ~np.isnan(exact)
+        for other in (short, unfinished):                       # (A): magnitudes and NaNs never move
+            assert np.array_equal(np.isnan(other), np.isnan(exact))
+            assert np.array_equal(np.abs(other)[ok].view(np.uint32), np.abs(exact)[ok].view(np.uint32))
+        sign_differences_without_the_finish += int((unfinished.view(np.uint32)[ok] != exact.view(np.uint32)[ok]).sum())
+        if key[1] <= 2:
+            assert_same_weights(short, exact, "%r, %d steps" % (key, steps))
+    assert sign_differences_without_the_finish > 0, "the population is meant to make the short form show"
