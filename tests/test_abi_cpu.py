@@ -53,6 +53,19 @@ def test_bad_shapes_are_errors_not_crashes():
     assert eng.shape_supported(eng.make_desc(0, 2, 2)) == 1
 
 
+def test_comm_family_argument_checks():
+    """srnn_comm_*: argument errors are status codes (checked before NCCL is even looked up); destroying NULL is a no-op."""
+    lib = eng.lib()
+    assert lib.srnn_comm_unique_id(None) == 1 and b"NULL" in lib.srnn_last_error_string()
+    comm = C.c_void_p()
+    assert lib.srnn_comm_init(None, C.c_int32(0), C.c_int32(1), C.byref(comm)) == 1
+    uid = (C.c_uint8 * 128)()
+    assert lib.srnn_comm_init(uid, C.c_int32(2), C.c_int32(2), C.byref(comm)) == 1      # rank out of range
+    assert b"rank" in lib.srnn_last_error_string()
+    assert lib.srnn_comm_allgather(None, None, None, C.c_int64(4), None) == 1
+    assert lib.srnn_comm_destroy(None) == 0
+
+
 def test_no_cpu_fallback():
     """Without a CUDA device the product path must refuse, not fall back."""
     import torch
